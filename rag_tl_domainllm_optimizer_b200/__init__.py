@@ -1,0 +1,16 @@
+"""B200-native exact dense retrieval: the FAISS-flat-shaped retrieval step of the reference's RAG loop.
+
+Public surface (mirrors ``faiss``): ``IndexFlatIP``, ``IndexFlatL2``, ``IndexFlat``, ``normalize_L2``,
+``METRIC_INNER_PRODUCT``, ``METRIC_L2``; plus ``ShardedIndexFlat`` (row-sharded over the GPUs of one box)
+and ``FlatRetriever`` (id -> passage text, producing the ``retrieved_docs`` lists the reference consumes).
+"""
+from ._lib import (ENGINE_AUTO, ENGINE_FMA, ENGINE_UMMA, METRIC_INNER_PRODUCT, METRIC_L2, B2RError)
+from .index import IndexFlat, IndexFlatIP, IndexFlatL2, ShapeError, cosine_rows, merge_packed, normalize_L2
+from .retriever import FlatRetriever, collate_retrieval_batch
+from .sharded import ShardedIndexFlat, shard_bounds
+
+__all__ = [
+    "IndexFlat", "IndexFlatIP", "IndexFlatL2", "normalize_L2", "METRIC_INNER_PRODUCT", "METRIC_L2", "ShapeError",
+    "B2RError", "ShardedIndexFlat", "shard_bounds", "FlatRetriever", "collate_retrieval_batch", "merge_packed",
+    "cosine_rows", "ENGINE_AUTO", "ENGINE_FMA", "ENGINE_UMMA",
+]

@@ -1,0 +1,670 @@
+// b2r_api.cu — the C ABI (include/b2r.h) over the sm_100a kernels.  No torch types, no CPU
+// fallback: every compute entry point needs a CUDA device and fails loudly without one.
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <float.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "../../include/b2r.h"
+#include "common.cuh"
+#include "finalize.cuh"
+#include "prep.cuh"
+#include "score_fma.cuh"
+#include "score_umma.cuh"
+
+using namespace b2r;
+
+// --------------------------------------------------------------------------------------
+// errors
+// --------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU_TRY(expr)                                                                              \
+  do {                                                                                            \
+    cudaError_t e_ = (expr);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(e_ == cudaErrorMemoryAllocation ? B2R_ERR_OOM : B2R_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, \
+                  cudaGetErrorString(e_), __FILE__, __LINE__);                                    \
+  } while (0)
+
+#define RC_TRY(expr)            \
+  do {                          \
+    int rc_ = (expr);           \
+    if (rc_ != B2R_OK) return rc_; \
+  } while (0)
+
+extern "C" const char* b2r_last_error(void) { return g_err.c_str(); }
+extern "C" const char* b2r_version(void) { return "b2r 0.1 sm_100a"; }
+extern "C" int b2r_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+// --------------------------------------------------------------------------------------
+// small helpers
+// --------------------------------------------------------------------------------------
+static bool is_device_ptr(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int ensure(size_t need) {
+    if (need <= bytes) return B2R_OK;
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+    size_t want = need + need / 4;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      e = cudaMalloc(&p, need);
+      want = need;
+    }
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+      return fail(B2R_ERR_OOM, "device allocation of %zu bytes failed", need);
+    }
+    bytes = want;
+    return B2R_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+};
+
+static int round_up(int v, int m) { return (v + m - 1) / m * m; }
+static int host_next_pow2(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+    ok = cudaSetDevice(dev) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// --------------------------------------------------------------------------------------
+// the handle
+// --------------------------------------------------------------------------------------
+struct b2r_index {
+  int64_t d = 0;
+  int metric = 0, storage = 0, device = 0;
+  int ld = 0;             // row pitch in elements (multiple of 64: one 128-byte TMA/UMMA swizzle row in bf16, two in fp32)
+  int64_t ntotal = 0, cap_rows = 0;
+  void* X = nullptr;      // [cap_rows][ld] fp32 or bf16
+  float* norm2 = nullptr; // [cap_rows] squared norm of the stored rows (L2 metric only)
+  float* maxnorm2 = nullptr;  // device scalar: largest stored squared norm
+  int sm_count = 148;
+  int engine = B2R_ENGINE_AUTO, pad = 6;
+  // per-search workspace
+  DevBuf qf, qh, qn2, thr, cand, cnt, stats, stage_q, stage_d, stage_i, stage_x, misc;
+  static constexpr int kEvPool = 256;           // scoring-kernel timers: one event pair per recent search
+  cudaEvent_t ev0[kEvPool] = {}, ev1[kEvPool] = {};
+  int64_t nrec = 0;                             // searches timed since the last timer reset
+  bool have_times = false;
+  b2r_search_stats last{};
+  UmmaState umma;         // tensor maps and scratch of the tcgen05 engine
+  std::mutex mu;
+  size_t elem_bytes() const { return storage == B2R_STORE_BF16 ? 2 : 4; }
+};
+
+extern "C" int b2r_index_create(b2r_index** out, int64_t d, int metric, int storage, int device) {
+  if (!out) return fail(B2R_ERR_ARG, "out is null");
+  *out = nullptr;
+  if (d <= 0 || d > 65536) return fail(B2R_ERR_ARG, "dimension %lld out of range (1..65536)", (long long)d);
+  if (metric != B2R_METRIC_IP && metric != B2R_METRIC_L2) return fail(B2R_ERR_ARG, "unknown metric %d", metric);
+  if (storage != B2R_STORE_F32 && storage != B2R_STORE_BF16) return fail(B2R_ERR_ARG, "unknown storage %d", storage);
+  int ndev = b2r_device_count();
+  if (ndev <= 0) return fail(B2R_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
+  if (device < 0 || device >= ndev) return fail(B2R_ERR_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  cudaDeviceProp prop;
+  CU_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(B2R_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+  b2r_index* idx = new (std::nothrow) b2r_index();
+  if (!idx) return fail(B2R_ERR_OOM, "host allocation failed");
+  idx->d = d;
+  idx->metric = metric;
+  idx->storage = storage;
+  idx->device = device;
+  idx->ld = round_up(int(d), 64);
+  idx->sm_count = prop.multiProcessorCount;
+  cudaError_t e = cudaMalloc(&idx->maxnorm2, sizeof(float));
+  if (e == cudaSuccess) e = cudaMemset(idx->maxnorm2, 0, sizeof(float));
+  for (int i = 0; i < b2r_index::kEvPool && e == cudaSuccess; ++i) {
+    e = cudaEventCreate(&idx->ev0[i]);
+    if (e == cudaSuccess) e = cudaEventCreate(&idx->ev1[i]);
+  }
+  if (e != cudaSuccess) {
+    delete idx;
+    return fail(B2R_ERR_CUDA, "handle set-up failed: %s", cudaGetErrorString(e));
+  }
+  *out = idx;
+  return B2R_OK;
+}
+
+extern "C" void b2r_index_free(b2r_index* idx) {
+  if (!idx) return;
+  DeviceGuard g(idx->device);
+  cudaDeviceSynchronize();
+  if (idx->X) cudaFree(idx->X);
+  if (idx->norm2) cudaFree(idx->norm2);
+  if (idx->maxnorm2) cudaFree(idx->maxnorm2);
+  DevBuf* bufs[] = {&idx->qf, &idx->qh, &idx->qn2, &idx->thr, &idx->cand, &idx->cnt, &idx->stats,
+                    &idx->stage_q, &idx->stage_d, &idx->stage_i, &idx->stage_x, &idx->misc};
+  for (DevBuf* b : bufs) b->release();
+  idx->umma.release();
+  for (int i = 0; i < b2r_index::kEvPool; ++i) {
+    if (idx->ev0[i]) cudaEventDestroy(idx->ev0[i]);
+    if (idx->ev1[i]) cudaEventDestroy(idx->ev1[i]);
+  }
+  delete idx;
+}
+
+static int grow(b2r_index* idx, int64_t rows, cudaStream_t st) {
+  if (rows <= idx->cap_rows) return B2R_OK;
+  int64_t want = rows;
+  if (idx->cap_rows > 0) want = std::max<int64_t>(rows, idx->cap_rows + idx->cap_rows / 2);
+  const size_t rowb = size_t(idx->ld) * idx->elem_bytes();
+  void* nx = nullptr;
+  cudaError_t e = cudaMalloc(&nx, size_t(want) * rowb);
+  if (e != cudaSuccess && want > rows) {
+    cudaGetLastError();
+    want = rows;
+    e = cudaMalloc(&nx, size_t(want) * rowb);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(B2R_ERR_OOM, "cannot allocate %zu bytes for %lld rows", size_t(want) * rowb, (long long)want);
+  }
+  float* nn = nullptr;
+  if (idx->metric == B2R_METRIC_L2) {
+    e = cudaMalloc(&nn, size_t(want) * sizeof(float));
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      cudaFree(nx);
+      return fail(B2R_ERR_OOM, "cannot allocate row norms for %lld rows", (long long)want);
+    }
+  }
+  if (idx->ntotal > 0) {
+    CU_TRY(cudaMemcpyAsync(nx, idx->X, size_t(idx->ntotal) * rowb, cudaMemcpyDeviceToDevice, st));
+    if (nn) CU_TRY(cudaMemcpyAsync(nn, idx->norm2, size_t(idx->ntotal) * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    CU_TRY(cudaStreamSynchronize(st));
+  }
+  if (idx->X) cudaFree(idx->X);
+  if (idx->norm2) cudaFree(idx->norm2);
+  idx->X = nx;
+  idx->norm2 = nn;
+  idx->cap_rows = want;
+  idx->umma.invalidate();
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_reserve(b2r_index* idx, int64_t n) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (n < 0) return fail(B2R_ERR_ARG, "negative row count");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  return grow(idx, n, nullptr);
+}
+
+extern "C" int b2r_index_add(b2r_index* idx, int64_t n, const float* x, int normalize, void* stream) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (n < 0) return fail(B2R_ERR_ARG, "negative row count");
+  if (n == 0) return B2R_OK;
+  if (!x) return fail(B2R_ERR_ARG, "x is null");
+  if (idx->ntotal + n > 0xfffffffeLL) return fail(B2R_ERR_LIMIT, "a shard holds at most 2^32-2 rows");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RC_TRY(grow(idx, idx->ntotal + n, st));
+  const bool dev_in = is_device_ptr(x);
+  const int64_t chunk = dev_in ? n : std::max<int64_t>(1, std::min<int64_t>(n, (int64_t(256) << 20) / (idx->d * 4)));
+  if (!dev_in) RC_TRY(idx->stage_x.ensure(size_t(chunk) * idx->d * 4));
+  for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+    const int64_t m = std::min(chunk, n - r0);
+    const float* src = x + r0 * idx->d;
+    if (!dev_in) {
+      CU_TRY(cudaMemcpyAsync(idx->stage_x.p, src, size_t(m) * idx->d * 4, cudaMemcpyHostToDevice, st));
+      src = static_cast<const float*>(idx->stage_x.p);
+    }
+    const int64_t row0 = idx->ntotal + r0;
+    const int blocks = int(std::min<int64_t>((m + 7) / 8, int64_t(idx->sm_count) * 16));
+    float* n2 = idx->norm2 ? idx->norm2 + row0 : nullptr;
+    if (idx->storage == B2R_STORE_BF16) {
+      __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(idx->X) + row0 * idx->ld;
+      ingest_rows_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(src, m, int(idx->d), dst, idx->ld, normalize, n2, idx->maxnorm2);
+    } else {
+      float* dst = static_cast<float*>(idx->X) + row0 * idx->ld;
+      ingest_rows_kernel<float><<<blocks, 256, 0, st>>>(src, m, int(idx->d), dst, idx->ld, normalize, n2, idx->maxnorm2);
+    }
+    CU_TRY(cudaGetLastError());
+    if (!dev_in) CU_TRY(cudaStreamSynchronize(st));  // the staging buffer is reused by the next chunk
+  }
+  idx->ntotal += n;
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_reset(b2r_index* idx) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  CU_TRY(cudaDeviceSynchronize());
+  idx->ntotal = 0;
+  CU_TRY(cudaMemset(idx->maxnorm2, 0, sizeof(float)));
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_ntotal(const b2r_index* idx, int64_t* out) {
+  if (!idx || !out) return fail(B2R_ERR_ARG, "null argument");
+  *out = idx->ntotal;
+  return B2R_OK;
+}
+
+template <typename T>
+__global__ void reconstruct_kernel(const T* row, int d, float* out) {
+  for (int j = threadIdx.x; j < d; j += blockDim.x) out[j] = ld_elem(row, j);
+}
+
+extern "C" int b2r_index_reconstruct(b2r_index* idx, int64_t i, float* out, void* stream) {
+  if (!idx || !out) return fail(B2R_ERR_ARG, "null argument");
+  if (i < 0 || i >= idx->ntotal) return fail(B2R_ERR_ARG, "row %lld out of range (ntotal %lld)", (long long)i, (long long)idx->ntotal);
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool dev_out = is_device_ptr(out);
+  float* dst = out;
+  if (!dev_out) {
+    RC_TRY(idx->misc.ensure(size_t(idx->d) * 4));
+    dst = static_cast<float*>(idx->misc.p);
+  }
+  if (idx->storage == B2R_STORE_BF16)
+    reconstruct_kernel<<<1, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(idx->X) + i * idx->ld, int(idx->d), dst);
+  else
+    reconstruct_kernel<<<1, 256, 0, st>>>(static_cast<const float*>(idx->X) + i * idx->ld, int(idx->d), dst);
+  CU_TRY(cudaGetLastError());
+  if (!dev_out) {
+    CU_TRY(cudaMemcpyAsync(out, dst, size_t(idx->d) * 4, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+  }
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_set_engine(b2r_index* idx, int engine) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (engine < B2R_ENGINE_AUTO || engine > B2R_ENGINE_UMMA) return fail(B2R_ERR_ARG, "unknown engine %d", engine);
+  idx->engine = engine;
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_set_pad(b2r_index* idx, int pad) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (pad < 0 || pad > 512) return fail(B2R_ERR_ARG, "pad %d out of range (0..512)", pad);
+  idx->pad = pad;
+  return B2R_OK;
+}
+
+// --------------------------------------------------------------------------------------
+// search
+// --------------------------------------------------------------------------------------
+static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, FinalizeParams& fp, int* launches) {
+  const int64_t ntiles = (idx->ntotal + kFmaTile - 1) / kFmaTile;
+  const int grid = int(std::max<int64_t>(1, std::min<int64_t>(ntiles, int64_t(idx->sm_count) * 2)));
+  const int cap = host_next_pow2(std::max(2 * kp, kp + 2 * kFmaTile));
+  const size_t smem = size_t(kFmaQB) * idx->ld * 4 + size_t(kFmaQB) * cap * 8;
+  if (smem > 227 * 1024)
+    return fail(B2R_ERR_LIMIT, "FMA engine needs %zu bytes of shared memory (d=%lld, k'=%d); limit is 232448", smem, (long long)idx->d, kp);
+  RC_TRY(idx->cand.ensure(size_t(grid) * nq * kp * 8));
+  FmaParams p{};
+  p.X = idx->X; p.n = idx->ntotal; p.ld = idx->ld; p.d = int(idx->d);
+  p.Q = static_cast<const float*>(idx->qf.p); p.ldq = idx->ld;
+  p.norm2 = idx->metric == B2R_METRIC_L2 ? idx->norm2 : nullptr;
+  p.thr = static_cast<uint32_t*>(idx->thr.p);
+  p.cand = static_cast<uint64_t*>(idx->cand.p);
+  p.nq = int(nq); p.kp = kp; p.cap = cap;
+  if (idx->storage == B2R_STORE_BF16)
+    CU_TRY(cudaFuncSetAttribute(score_fma_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  else
+    CU_TRY(cudaFuncSetAttribute(score_fma_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  for (int64_t q0 = 0; q0 < nq; q0 += kFmaQB) {
+    p.q0 = int(q0);
+    p.nqb = int(std::min<int64_t>(kFmaQB, nq - q0));
+    if (idx->storage == B2R_STORE_BF16)
+      score_fma_kernel<__nv_bfloat16><<<grid, kFmaWarps * 32, smem, st>>>(p);
+    else
+      score_fma_kernel<float><<<grid, kFmaWarps * 32, smem, st>>>(p);
+    ++*launches;
+  }
+  CU_TRY(cudaGetLastError());
+  fp.cand = p.cand;
+  fp.slot_stride = int64_t(nq) * kp;
+  fp.q_stride = kp;
+  fp.nslots = grid;
+  fp.per = kp;
+  fp.cnt = nullptr;
+  fp.errfac = float((double(idx->d) + 8.0) * 6.1e-8);   // (d+8) * 2^-24 * 1.02
+  return B2R_OK;
+}
+
+static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t k, int normalize_queries,
+                         int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st) {
+  const int kp = int(std::min<int64_t>(k + idx->pad, 2048));
+  int launches = 0;
+  const int ldq = idx->ld;
+  RC_TRY(idx->qf.ensure(size_t(nq) * ldq * 4));
+  RC_TRY(idx->qh.ensure(size_t(nq + 256) * ldq * 2));
+  RC_TRY(idx->qn2.ensure(size_t(nq) * 4));
+  RC_TRY(idx->thr.ensure(size_t(nq) * 4));
+  RC_TRY(idx->stats.ensure(2 * sizeof(unsigned long long)));
+  CU_TRY(cudaMemsetAsync(idx->thr.p, 0, size_t(nq) * 4, st));
+  CU_TRY(cudaMemsetAsync(idx->stats.p, 0, 2 * sizeof(unsigned long long), st));
+  {
+    const int blocks = int(std::min<int64_t>((nq + 7) / 8, int64_t(idx->sm_count) * 8));
+    prep_queries_kernel<<<blocks, 256, 0, st>>>(q_dev, nq, int(idx->d), ldq, normalize_queries,
+                                                idx->storage == B2R_STORE_BF16, static_cast<float*>(idx->qf.p),
+                                                idx->storage == B2R_STORE_BF16 ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
+                                                static_cast<float*>(idx->qn2.p));
+    CU_TRY(cudaGetLastError());
+    ++launches;
+  }
+  FinalizeParams fp{};
+  int engine_used = B2R_ENGINE_FMA;
+  if (idx->ntotal > 0) {
+    const int slot = int(idx->nrec % b2r_index::kEvPool);
+    CU_TRY(cudaEventRecord(idx->ev0[slot], st));
+    bool use_umma = false;
+    if (idx->engine != B2R_ENGINE_FMA) {
+      use_umma = umma_supported(idx->storage, int(idx->d), kp, idx->ntotal);
+      if (!use_umma && idx->engine == B2R_ENGINE_UMMA)
+        return fail(B2R_ERR_LIMIT, "the tcgen05 engine does not take this shape (storage %d, d %lld, k' %d)", idx->storage, (long long)idx->d, kp);
+    }
+    if (use_umma) {
+      UmmaCall uc{};
+      uc.X = idx->X; uc.n = idx->ntotal; uc.ld = idx->ld; uc.d = int(idx->d); uc.storage = idx->storage;
+      uc.Qh = idx->qh.p; uc.Qf = static_cast<const float*>(idx->qf.p); uc.nq = int(nq); uc.kp = kp;
+      uc.norm2 = idx->metric == B2R_METRIC_L2 ? idx->norm2 : nullptr;
+      uc.thr = static_cast<uint32_t*>(idx->thr.p);
+      uc.sm_count = idx->sm_count;
+      std::string err;
+      int rc = umma_launch(idx->umma, uc, st, fp, &launches, err);
+      if (rc != B2R_OK) return fail(rc, "%s", err.c_str());
+      engine_used = B2R_ENGINE_UMMA;
+    } else {
+      RC_TRY(launch_fma(idx, nq, kp, st, fp, &launches));
+    }
+    CU_TRY(cudaEventRecord(idx->ev1[slot], st));
+    ++idx->nrec;
+    idx->have_times = true;
+  } else {
+    idx->have_times = false;
+    fp.nslots = 0;
+    fp.per = 1;
+  }
+  fp.thr = static_cast<const uint32_t*>(idx->thr.p);
+  fp.nq = int(nq); fp.kp = kp; fp.k = int(k);
+  fp.sortn = std::max(2048, host_next_pow2(2 * kp));
+  fp.X = idx->X; fp.ld = idx->ld; fp.d = int(idx->d); fp.storage = idx->storage;
+  fp.Q = static_cast<const float*>(idx->qf.p); fp.ldq = ldq; fp.qn2 = static_cast<const float*>(idx->qn2.p);
+  fp.metric = idx->metric; fp.n = idx->ntotal; fp.row_offset = row_offset;
+  fp.maxnorm2 = idx->maxnorm2;
+  fp.D = D; fp.I = I; fp.packed = packed;
+  fp.stats = static_cast<unsigned long long*>(idx->stats.p);
+  const size_t smem = size_t(fp.sortn + host_next_pow2(kp)) * 8;
+  if (idx->storage == B2R_STORE_BF16) {
+    CU_TRY(cudaFuncSetAttribute(finalize_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    finalize_kernel<__nv_bfloat16><<<int(nq), 256, smem, st>>>(fp);
+  } else {
+    CU_TRY(cudaFuncSetAttribute(finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    finalize_kernel<float><<<int(nq), 256, smem, st>>>(fp);
+  }
+  CU_TRY(cudaGetLastError());
+  ++launches;
+  idx->last = b2r_search_stats{};
+  idx->last.nq = nq; idx->last.k = k; idx->last.kprime = kp;
+  idx->last.engine = engine_used; idx->last.launches = launches;
+  return B2R_OK;
+}
+
+static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries, int64_t row_offset,
+                      float* D, int64_t* I, uint64_t* packed, void* stream) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (nq < 0) return fail(B2R_ERR_ARG, "negative query count");
+  if (k <= 0) return fail(B2R_ERR_ARG, "k must be positive (got %lld)", (long long)k);
+  if (k > 1024) return fail(B2R_ERR_LIMIT, "k=%lld exceeds the supported maximum of 1024", (long long)k);
+  if (nq == 0) return B2R_OK;
+  if (nq > (int64_t(1) << 22)) return fail(B2R_ERR_LIMIT, "at most 2^22 queries per call");
+  if (!q) return fail(B2R_ERR_ARG, "q is null");
+  if (packed ? false : (!D || !I)) return fail(B2R_ERR_ARG, "D or I is null");
+  if (idx->ntotal + row_offset > 0xfffffffeLL || row_offset < 0) return fail(B2R_ERR_LIMIT, "global ids must stay below 2^32-1");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool q_dev = is_device_ptr(q);
+  const bool out_dev = packed ? true : is_device_ptr(D);
+  if (!packed && out_dev != is_device_ptr(I)) return fail(B2R_ERR_ARG, "D and I must both be host or both be device pointers");
+  if (packed && !is_device_ptr(packed)) return fail(B2R_ERR_ARG, "packed must be a device pointer");
+  const float* qd = q;
+  if (!q_dev) {
+    RC_TRY(idx->stage_q.ensure(size_t(nq) * idx->d * 4));
+    CU_TRY(cudaMemcpyAsync(idx->stage_q.p, q, size_t(nq) * idx->d * 4, cudaMemcpyHostToDevice, st));
+    qd = static_cast<const float*>(idx->stage_q.p);
+  }
+  float* Dd = D;
+  int64_t* Id = I;
+  if (!packed && !out_dev) {
+    RC_TRY(idx->stage_d.ensure(size_t(nq) * k * 4));
+    RC_TRY(idx->stage_i.ensure(size_t(nq) * k * 8));
+    Dd = static_cast<float*>(idx->stage_d.p);
+    Id = static_cast<int64_t*>(idx->stage_i.p);
+  }
+  RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st));
+  if (!packed && !out_dev) {
+    CU_TRY(cudaMemcpyAsync(D, Dd, size_t(nq) * k * 4, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(I, Id, size_t(nq) * k * 8, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+  } else if (!q_dev) {
+    CU_TRY(cudaStreamSynchronize(st));  // the caller may reuse its host query buffer
+  }
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_search(b2r_index* idx, int64_t nq, const float* q, int64_t k, float* D, int64_t* I, void* stream) {
+  return search_any(idx, nq, q, k, 0, 0, D, I, nullptr, stream);
+}
+extern "C" int b2r_index_search_ex(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries,
+                                   int64_t row_offset, float* D, int64_t* I, void* stream) {
+  return search_any(idx, nq, q, k, normalize_queries, row_offset, D, I, nullptr, stream);
+}
+extern "C" int b2r_index_search_packed(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries,
+                                       int64_t row_offset, uint64_t* packed, void* stream) {
+  if (!packed) return fail(B2R_ERR_ARG, "packed is null");
+  return search_any(idx, nq, q, k, normalize_queries, row_offset, nullptr, nullptr, packed, stream);
+}
+
+extern "C" int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed, float* D,
+                                int64_t* I, int device, void* stream) {
+  if (metric != B2R_METRIC_IP && metric != B2R_METRIC_L2) return fail(B2R_ERR_ARG, "unknown metric %d", metric);
+  if (G <= 0 || nq < 0 || k <= 0) return fail(B2R_ERR_ARG, "bad shape G=%lld nq=%lld k=%lld", (long long)G, (long long)nq, (long long)k);
+  if (k > 1024) return fail(B2R_ERR_LIMIT, "k=%lld exceeds the supported maximum of 1024", (long long)k);
+  if (nq == 0) return B2R_OK;
+  if (!packed || !D || !I) return fail(B2R_ERR_ARG, "null argument");
+  if (b2r_device_count() <= 0) return fail(B2R_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
+  if (!is_device_ptr(packed) || !is_device_ptr(D) || !is_device_ptr(I)) return fail(B2R_ERR_ARG, "packed, D and I must be device pointers");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int sortn = std::max(2048, host_next_pow2(int(2 * k)));
+  merge_packed_kernel<<<int(nq), 256, size_t(sortn) * 8, st>>>(packed, int(G), int(nq), int(k), sortn, metric, D, I);
+  CU_TRY(cudaGetLastError());
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_last_stats(b2r_index* idx, b2r_search_stats* out) {
+  if (!idx || !out) return fail(B2R_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  unsigned long long h[2] = {0, 0};
+  if (idx->stats.p) {
+    CU_TRY(cudaDeviceSynchronize());
+    CU_TRY(cudaMemcpy(h, idx->stats.p, sizeof h, cudaMemcpyDeviceToHost));
+  }
+  idx->last.unverified = int64_t(h[0]);
+  idx->last.candidates = int64_t(h[1]);
+  *out = idx->last;
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_last_score_ms(b2r_index* idx, float* ms) {
+  if (!idx || !ms) return fail(B2R_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  *ms = 0.f;
+  if (!idx->have_times) return B2R_OK;
+  const int slot = int((idx->nrec - 1) % b2r_index::kEvPool);
+  CU_TRY(cudaEventSynchronize(idx->ev1[slot]));
+  CU_TRY(cudaEventElapsedTime(ms, idx->ev0[slot], idx->ev1[slot]));
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_score_time(b2r_index* idx, int reset, double* total_ms, int64_t* nsearch) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  const int64_t cnt = std::min<int64_t>(idx->nrec, b2r_index::kEvPool);
+  double sum = 0.0;
+  for (int64_t i = 0; i < cnt; ++i) {
+    const int slot = int((idx->nrec - 1 - i) % b2r_index::kEvPool);
+    float ms = 0.f;
+    CU_TRY(cudaEventSynchronize(idx->ev1[slot]));
+    CU_TRY(cudaEventElapsedTime(&ms, idx->ev0[slot], idx->ev1[slot]));
+    sum += ms;
+  }
+  if (total_ms) *total_ms = sum;
+  if (nsearch) *nsearch = cnt;
+  if (reset) { idx->nrec = 0; idx->have_times = false; }
+  return B2R_OK;
+}
+
+// --------------------------------------------------------------------------------------
+// stand-alone kernels
+// --------------------------------------------------------------------------------------
+extern "C" int b2r_normalize_l2(int64_t n, int64_t d, float* x, int device, void* stream) {
+  if (n < 0 || d <= 0 || d > 65536) return fail(B2R_ERR_ARG, "bad shape n=%lld d=%lld", (long long)n, (long long)d);
+  if (n == 0) return B2R_OK;
+  if (!x) return fail(B2R_ERR_ARG, "x is null");
+  if (b2r_device_count() <= 0) return fail(B2R_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool dev = is_device_ptr(x);
+  float* xd = x;
+  if (!dev) {
+    CU_TRY(cudaMalloc(&xd, size_t(n) * d * 4));
+    cudaError_t e = cudaMemcpyAsync(xd, x, size_t(n) * d * 4, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) { cudaFree(xd); return fail(B2R_ERR_CUDA, "H2D copy failed: %s", cudaGetErrorString(e)); }
+  }
+  int sm = 148;
+  cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device);
+  const int blocks = int(std::min<int64_t>((n + 7) / 8, int64_t(sm) * 16));
+  normalize_inplace_kernel<<<blocks, 256, 0, st>>>(xd, n, int(d));
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && !dev) {
+    e = cudaMemcpyAsync(x, xd, size_t(n) * d * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  }
+  if (!dev) cudaFree(xd);
+  if (e != cudaSuccess) return fail(B2R_ERR_CUDA, "normalize_l2 failed: %s", cudaGetErrorString(e));
+  return B2R_OK;
+}
+
+extern "C" int b2r_cosine_rows(int64_t n, int64_t m, int64_t d, const float* resp, const float* docs, float* cosout,
+                               float* maxcos, int device, void* stream) {
+  if (n < 0 || m < 0 || d <= 0) return fail(B2R_ERR_ARG, "bad shape n=%lld m=%lld d=%lld", (long long)n, (long long)m, (long long)d);
+  if (n == 0) return B2R_OK;
+  if (!resp || !maxcos || (m > 0 && !docs)) return fail(B2R_ERR_ARG, "null argument");
+  if (b2r_device_count() <= 0) return fail(B2R_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool dev = is_device_ptr(resp);
+  if (m > 0 && dev != is_device_ptr(docs)) return fail(B2R_ERR_ARG, "resp and docs must both be host or both be device pointers");
+  if (dev != is_device_ptr(maxcos) || (cosout && dev != is_device_ptr(cosout)))
+    return fail(B2R_ERR_ARG, "outputs must live where the inputs live");
+  const size_t br = size_t(n) * d * 4, bd = size_t(n) * m * d * 4, bc = size_t(n) * m * 4, bm = size_t(n) * 4;
+  char* ws = nullptr;
+  // layout: [maxord n*4][resp][docs][cos][maxcos] (the last four only for host callers)
+  const size_t total = bm + (dev ? 0 : br + bd + bc + bm);
+  CU_TRY(cudaMalloc(&ws, std::max<size_t>(total, 16)));
+  uint32_t* maxord = reinterpret_cast<uint32_t*>(ws);
+  const float* r_d = resp; const float* d_d = docs; float* c_d = cosout; float* m_d = maxcos;
+  cudaError_t e = cudaMemsetAsync(maxord, 0, bm, st);
+  if (!dev) {
+    float* rr = reinterpret_cast<float*>(ws + bm);
+    float* dd = reinterpret_cast<float*>(ws + bm + br);
+    c_d = reinterpret_cast<float*>(ws + bm + br + bd);
+    m_d = reinterpret_cast<float*>(ws + bm + br + bd + bc);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rr, resp, br, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && m > 0) e = cudaMemcpyAsync(dd, docs, bd, cudaMemcpyHostToDevice, st);
+    r_d = rr; d_d = dd;
+  }
+  if (e == cudaSuccess && m > 0) {
+    int sm = 148;
+    cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device);
+    const int blocks = int(std::min<int64_t>((n * m + 7) / 8, int64_t(sm) * 16));
+    cosine_rows_kernel<<<blocks, 256, 0, st>>>(r_d, d_d, n, m, int(d), (dev && !cosout) ? nullptr : c_d, maxord);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) {
+    finish_maxcos_kernel<<<int((n + 255) / 256), 256, 0, st>>>(maxord, n, m_d);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess && !dev) {
+    if (cosout && m > 0) e = cudaMemcpyAsync(cosout, c_d, bc, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(maxcos, m_d, bm, cudaMemcpyDeviceToHost, st);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(ws);
+  if (e != cudaSuccess) return fail(B2R_ERR_CUDA, "cosine_rows failed: %s", cudaGetErrorString(e));
+  return B2R_OK;
+}

@@ -1,0 +1,173 @@
+// prep.cuh — kernel (a): L2-normalise / cast, one warp per row, 128-bit coalesced loads.
+//
+// Replaces faiss normalize_L2 / the normalize() inside sklearn cosine_similarity that the
+// reference calls at reinforcement_learning_optimization_after_rag.py:70,78,104
+// (zero-norm rows stay unchanged, as sklearn's _handle_zeros_in_scale does).
+//
+// Arithmetic (restated bit for bit by oracle/flat_oracle.c: b2r_oracle_normalize):
+//   ss   = DOT64 sum of squares of the fp32 row            (common.cuh)
+//   nrm  = (float) sqrt(ss)                                (IEEE fp64 sqrt, RN to fp32)
+//   y_j  = nrm == 0 ? x_j : x_j / nrm                      (IEEE fp32 division)
+//   bf16 storage then rounds y_j to nearest-even bf16.
+// HBM bytes per row: d*4 read + d*s written (s = 4 or 2) + 4 (norm).
+#pragma once
+#include "common.cuh"
+
+namespace b2r {
+
+__device__ __forceinline__ void st_elem(float* p, int64_t i, float v) { p[i] = v; }
+__device__ __forceinline__ void st_elem(__nv_bfloat16* p, int64_t i, float v) { p[i] = __float2bfloat16_rn(v); }
+__device__ __forceinline__ float round_store(float v, float*) { return v; }
+__device__ __forceinline__ float round_store(float v, __nv_bfloat16*) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+// Rows of `in` ([n,d] fp32, pitch d, possibly unaligned) -> rows of `out` (pitch ld >= d,
+// 16B-aligned rows, zero padded to ld).  norm2[r] (optional) = squared norm of the STORED row
+// (after normalisation and rounding), as fp32 of its DOT64 value; maxnorm2 (optional) is
+// raised to the largest of them with an integer atomicMax (non-negative floats order as ints).
+template <typename TOut>
+__global__ void __launch_bounds__(256) ingest_rows_kernel(const float* __restrict__ in, int64_t n, int d,
+                                                          TOut* __restrict__ out, int ld, int normalize,
+                                                          float* __restrict__ norm2, float* __restrict__ maxnorm2) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  const bool vec_in = ((d & 3) == 0) && ((reinterpret_cast<uintptr_t>(in) & 15) == 0);
+  float wmax = 0.f;
+  for (int64_t r = warp0; r < n; r += nwarps) {
+    const float* x = in + r * int64_t(d);
+    TOut* y = out + r * int64_t(ld);
+    float nrm = 1.f;
+    if (normalize) {
+      double ss = vec_in ? warp_reduce64<Red::kDot>(x, x, d, lane) : warp_reduce64_unaligned<Red::kDot>(x, x, d, lane);
+      nrm = float(sqrt(ss));
+      if (nrm == 0.f) nrm = 1.f;
+    }
+    // write the stored row, accumulate its squared norm in the same DOT64 order
+    double acc = 0.0;
+    for (int c = lane * 4; c < ld; c += 128) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c + 4 <= d && vec_in) {
+        v = ld4(x + c);
+      } else {
+        if (c + 0 < d) v.x = x[c + 0];
+        if (c + 1 < d) v.y = x[c + 1];
+        if (c + 2 < d) v.z = x[c + 2];
+        if (c + 3 < d) v.w = x[c + 3];
+      }
+      if (normalize) { v.x = v.x / nrm; v.y = v.y / nrm; v.z = v.z / nrm; v.w = v.w / nrm; }
+      v.x = round_store(v.x, y); v.y = round_store(v.y, y); v.z = round_store(v.z, y); v.w = round_store(v.w, y);
+      st4(y + c, v);
+      if (c + 0 < d) acc = fma(double(v.x), double(v.x), acc);
+      if (c + 1 < d) acc = fma(double(v.y), double(v.y), acc);
+      if (c + 2 < d) acc = fma(double(v.z), double(v.z), acc);
+      if (c + 3 < d) acc = fma(double(v.w), double(v.w), acc);
+    }
+    acc = butterfly64(acc);
+    float n2 = float(acc);
+    if (norm2 && lane == 0) norm2[r] = n2;
+    wmax = fmaxf(wmax, n2);
+  }
+  if (maxnorm2 && lane == 0 && wmax > 0.f) atomicMax(reinterpret_cast<int*>(maxnorm2), __float_as_int(wmax));
+}
+
+// In-place normalisation of caller-owned [n,d] fp32 (pitch d; any alignment).
+__global__ void __launch_bounds__(256) normalize_inplace_kernel(float* __restrict__ x, int64_t n, int d) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  const bool vec = ((d & 3) == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+  for (int64_t r = warp0; r < n; r += nwarps) {
+    float* row = x + r * int64_t(d);
+    double ss = vec ? warp_reduce64<Red::kDot>(row, row, d, lane) : warp_reduce64_unaligned<Red::kDot>(row, row, d, lane);
+    float nrm = float(sqrt(ss));
+    if (nrm == 0.f) continue;
+    if (vec) {
+      for (int c = lane * 4; c < d; c += 128) {
+        float4 v = ld4(row + c);
+        v.x = v.x / nrm; v.y = v.y / nrm; v.z = v.z / nrm; v.w = v.w / nrm;
+        st4(row + c, v);
+      }
+    } else {
+      for (int j = lane; j < d; j += 32) row[j] = row[j] / nrm;
+    }
+  }
+}
+
+// Batched reward cosine (reference :63-79, :99-104).
+//   cos(i,j) = (float)( dot64 / (sqrt(ssa) * sqrt(ssb)) ), a zero norm counts as 1
+// one warp per (sample i, doc j); maxcos[i] is reduced by a second tiny kernel-free step:
+// each warp raises an ordered-uint atomicMax, decoded by finish_maxcos_kernel.
+__global__ void __launch_bounds__(256) cosine_rows_kernel(const float* __restrict__ resp, const float* __restrict__ docs,
+                                                          int64_t n, int64_t m, int d, float* __restrict__ cosout,
+                                                          uint32_t* __restrict__ maxord) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t p = warp0; p < n * m; p += nwarps) {
+    int64_t i = p / m;
+    const float* a = resp + i * int64_t(d);
+    const float* b = docs + p * int64_t(d);
+    double dot = warp_reduce64_unaligned<Red::kDot>(a, b, d, lane);
+    double sa = warp_reduce64_unaligned<Red::kDot>(a, a, d, lane);
+    double sb = warp_reduce64_unaligned<Red::kDot>(b, b, d, lane);
+    double na = sqrt(sa), nb = sqrt(sb);
+    if (na == 0.0) na = 1.0;
+    if (nb == 0.0) nb = 1.0;
+    float c = float(dot / (na * nb));
+    if (lane == 0) {
+      if (cosout) cosout[p] = c;
+      if (maxord) atomicMax(maxord + i, f32_to_ordered(c));
+    }
+  }
+}
+__global__ void finish_maxcos_kernel(const uint32_t* __restrict__ maxord, int64_t n, float* __restrict__ maxcos) {
+  int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) maxcos[i] = maxord[i] == 0u ? 0.0f : ordered_to_f32(maxord[i]);
+}
+
+// Query preparation: [nq,d] fp32 (pitch d) -> qf fp32 [nq,ldq] (normalised if asked, rounded to
+// bf16 values in fast mode, zero padded), optional bf16 copy qh [nq,ldq], qn2[q] = squared norm
+// of the prepared query (fp32 of DOT64).  One warp per query.
+__global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, int64_t nq, int d, int ldq,
+                                                           int normalize, int round_bf16, float* __restrict__ qf,
+                                                           __nv_bfloat16* __restrict__ qh, float* __restrict__ qn2) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t r = warp0; r < nq; r += nwarps) {
+    const float* x = q + r * int64_t(d);
+    float nrm = 1.f;
+    if (normalize) {
+      double ss = warp_reduce64_unaligned<Red::kDot>(x, x, d, lane);
+      nrm = float(sqrt(ss));
+      if (nrm == 0.f) nrm = 1.f;
+    }
+    double acc = 0.0;
+    for (int c = lane * 4; c < ldq; c += 128) {
+      float v[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        float e = (c + t < d) ? x[c + t] : 0.f;
+        if (normalize) e = e / nrm;
+        if (round_bf16) e = __bfloat162float(__float2bfloat16_rn(e));
+        v[t] = e;
+        if (c + t < d) acc = fma(double(e), double(e), acc);
+      }
+      st4(qf + r * int64_t(ldq) + c, make_float4(v[0], v[1], v[2], v[3]));
+      if (qh) st4(qh + r * int64_t(ldq) + c, make_float4(v[0], v[1], v[2], v[3]));
+    }
+    acc = butterfly64(acc);
+    if (lane == 0) qn2[r] = float(acc);
+  }
+}
+
+}  // namespace b2r
