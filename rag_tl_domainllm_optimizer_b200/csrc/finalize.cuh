@@ -23,7 +23,11 @@ struct FinalizeParams {
   int64_t q_stride;        // elements between consecutive queries inside a slot
   int nslots;
   int per;                 // entries to scan per (slot, query)
-  const uint32_t* cnt;     // optional valid-entry counts [nslots][nq]; nullptr = scan `per`, skip zeros
+  const uint32_t* cnt;     // optional valid-entry counts; nullptr = scan `per`, skip zeros
+  int interleave;          // 0: cand[slot*slot_stride + q*q_stride + i], cnt[slot*nq + q]
+                           // 128 (tcgen05 engine): queries are grouped in launches of `qchunk` and tiles of 128;
+                           //   cand[(((l*nslots + slot)*mt_max + m)*per + i)*128 + t], cnt[((l*nslots + slot)*mt_max + m)*128 + t]
+  int mt_max, qchunk;
   const uint32_t* thr;     // optional ordered-float thresholds [nq] (0 = none)
   int nq, kp, k, sortn;
   const void* X; int ld; int d; int storage;
@@ -81,10 +85,18 @@ __global__ void __launch_bounds__(256) finalize_kernel(FinalizeParams p) {
   const T* X = reinterpret_cast<const T*>(p.X);
 
   const uint32_t thrq = p.thr ? p.thr[q] : 0u;
+  const int ql = p.interleave ? q % p.qchunk : 0, lq = p.interleave ? q / p.qchunk : 0;
   auto fetch = [&](int64_t e) -> uint64_t {
     int slot = int(e / p.per), i = int(e % p.per);
-    if (p.cnt && uint32_t(i) >= p.cnt[int64_t(slot) * p.nq + q]) return 0ull;
-    uint64_t key = p.cand[slot * p.slot_stride + q * p.q_stride + i];
+    uint64_t key;
+    if (p.interleave) {
+      const size_t blk = (size_t(lq) * p.nslots + slot) * p.mt_max + (ql >> 7);
+      if (uint32_t(i) >= p.cnt[blk * 128 + (ql & 127)]) return 0ull;
+      key = p.cand[(blk * p.per + i) * 128 + (ql & 127)];
+    } else {
+      if (p.cnt && uint32_t(i) >= p.cnt[int64_t(slot) * p.nq + q]) return 0ull;
+      key = p.cand[slot * p.slot_stride + q * p.q_stride + i];
+    }
     return (uint32_t(key >> 32) >= thrq) ? key : 0ull;
   };
   const int ncand = stream_topk(s, p.sortn, p.kp, int64_t(p.nslots) * p.per, fetch, &fill_s, p.stats ? p.stats + 1 : nullptr);

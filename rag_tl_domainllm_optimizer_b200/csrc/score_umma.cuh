@@ -1,13 +1,396 @@
-// score_umma.cuh — kernel (b), tensor-core variant (placeholder until the tcgen05 kernel lands).
+// score_umma.cuh — kernel (b), tensor-core variant: TMA -> shared memory -> tcgen05.mma -> TMEM ->
+// threshold-filtered running top-K' in the epilogue.  The [B,N] score matrix never reaches HBM.
+//
+// One persistent CTA per SM, 6 warps:
+//   warp 0      TMA producer   : per K-step one 128-row query box (A) and one 256-row corpus box (B),
+//                                128 bytes of K per row, SWIZZLE_128B, 4-stage mbarrier ring
+//   warp 1      MMA issuer     : one elected lane issues 4 x tcgen05.mma (M=128, N=256, 32 B of K each) per
+//                                stage into one of two 256-column TMEM accumulators; tcgen05.commit frees
+//                                the smem stage and, after the last K-step, hands the accumulator over
+//   warps 2..5  epilogue       : thread = one query (TMEM lane), tcgen05.ld 32 columns at a time; a score
+//                                is kept only if it beats the query's running threshold (>99% fail this one
+//                                compare); survivors are appended to the (CTA, query) candidate buffer.
+// Tile (m, n) = queries [128m, 128m+128) x corpus rows [256n, 256n+256); a CTA owns a contiguous range of n
+// and loops m inside it (corpus re-reads of the inner loop hit L2).
+//
+// Running top-K': threshold + append buffer (cap entries per (CTA, query), interleaved [entry][lane] so that a
+// warp's accesses coalesce).  First tile of a query: the threshold is found by bisection over the 256 scores
+// while they still sit in TMEM (no memory traffic).  When a buffer is nearly full the owning lane selects a
+// new threshold by bisection on the packed keys (lane-parallel: all lanes of a warp compact their own buffers
+// at once), keeps [K', kmax] entries and publishes the bound with a global atomicMax, so all 148 CTAs filter
+// with the best bound any of them has found.  A published bound is always the K'-th best score of a real
+// subset of rows, hence a valid lower bound of the final K'-th best.
+//
+// Algorithmic HBM bytes per search: rows * ld * sizeof(elem) (the corpus shard, once).
+// Algorithmic flops: 2 * nq * rows * d.
 #pragma once
+#include <cuda.h>
 #include <string>
 #include "common.cuh"
 #include "finalize.cuh"
 
 namespace b2r {
 
+constexpr int kUmBM = 128;          // queries per tile (MMA M)
+constexpr int kUmBN = 256;          // corpus rows per tile (MMA N)
+constexpr int kUmStages = 4;
+constexpr int kUmRowBytes = 128;    // bytes of K per row per stage (one swizzle atom)
+constexpr int kUmABytes = kUmBM * kUmRowBytes;        // 16 KB
+constexpr int kUmBBytes = kUmBN * kUmRowBytes;        // 32 KB
+constexpr int kUmStageBytes = kUmABytes + kUmBBytes;  // 48 KB
+constexpr int kUmQMax = 2048;       // queries per launch (thresholds / counters live in shared memory)
+constexpr int kUmThreads = 192;
+constexpr int kUmSmemState = kUmStages * kUmStageBytes;                 // thr_s follows the stages
+constexpr int kUmSmemBytes = kUmSmemState + kUmQMax * 8 + kUmBN * 4 + 256 + 1024;  // + alignment slack
+
+struct UmmaParams {
+  int64_t n;          // rows of the shard
+  int64_t row0;       // first row covered by this launch (tiles start here; multiple of 256)
+  int64_t ntiles;     // corpus tiles covered by this launch
+  int nq;             // queries in this launch
+  int q0;             // index of the first query of this launch in the whole call
+  int mtiles;
+  int mt_stride;      // m-tiles per CTA slot in the scratch layout (>= mtiles)
+  int num_k;          // K steps per tile
+  int kp, cap, kmax;
+  const float* norm2; // L2 metric: |x|^2 per stored row
+  uint32_t* thr_g;    // [call nq] ordered-float thresholds shared by all CTAs (0 = none yet)
+  uint64_t* cand;     // [grid][mtiles][cap][128]
+  uint32_t* cnt;      // [grid][mtiles*128]
+  uint32_t idesc;
+  float* dbg;         // optional [nq][n] dense scores (probe only)
+};
+
+// ---------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tmap, uint32_t bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const CUtensorMap* tmap, uint32_t bar, int c0, int c1, uint64_t hint) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "l"(hint) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+template <bool kTf32>
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  if (kTf32) {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+  } else {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+// 32 consecutive fp32 columns of this thread's TMEM lane; returns after the data is in registers.
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&u)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]),
+        "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15]), "=r"(u[16]),
+        "=r"(u[17]), "=r"(u[18]), "=r"(u[19]), "=r"(u[20]), "=r"(u[21]), "=r"(u[22]), "=r"(u[23]), "=r"(u[24]),
+        "=r"(u[25]), "=r"(u[26]), "=r"(u[27]), "=r"(u[28]), "=r"(u[29]), "=r"(u[30]), "=r"(u[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (tcgen05 "smem descriptor"):
+//   bits [0,14) start address >> 4, [16,30) leading byte offset >> 4 (unused for swizzled K-major: 1),
+//   [32,46) stride byte offset >> 4 (8 rows x 128 B = 1024 B), [46,48) version = 1, [61,64) layout 2 = 128B swizzle.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+  uint64_t d = uint64_t((saddr & 0x3ffffu) >> 4);
+  d |= uint64_t(1) << 16;
+  d |= uint64_t(1024 >> 4) << 32;
+  d |= uint64_t(1) << 46;
+  d |= uint64_t(2) << 61;
+  return d;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// lane-parallel compaction of (CTA, query) candidate buffers (entries at buf[e * 128])
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void compact_lanes(uint64_t* buf, uint32_t& cnt, float& thr, int kp, int kmax,
+                                              uint32_t* thr_g_q, bool need) {
+  const uint32_t n = need ? cnt : 0u;
+  uint64_t mn = ~0ull, mx = 0ull;
+  for (uint32_t e = 0; e < n; ++e) {
+    uint64_t k = buf[size_t(e) * 128];
+    mn = k < mn ? k : mn;
+    mx = k > mx ? k : mx;
+  }
+  uint64_t lo = mn, hi = mx;
+  uint32_t clo = n;
+  // invariant: count(key >= lo) == clo >= kp, count(key >= hi + 1) < kp
+  while (__any_sync(kFull, need && clo > uint32_t(kmax) && hi > lo)) {
+    const bool act = need && clo > uint32_t(kmax) && hi > lo;
+    const uint64_t mid = lo + ((hi - lo) >> 1) + 1;   // lo < mid <= hi
+    uint32_t c = 0;
+    const uint32_t nn = act ? n : 0u;
+#pragma unroll 4
+    for (uint32_t e = 0; e < nn; ++e) c += (buf[size_t(e) * 128] >= mid) ? 1u : 0u;
+    if (act) {
+      if (c >= uint32_t(kp)) { lo = mid; clo = c; } else { hi = mid - 1; }
+    }
+  }
+  if (need) {
+    uint32_t w = 0;
+    for (uint32_t e = 0; e < n; ++e) {
+      uint64_t k = buf[size_t(e) * 128];
+      if (k >= lo) { buf[size_t(w) * 128] = k; ++w; }
+    }
+    cnt = w;
+    thr = fmaxf(thr, key_score_max(lo));
+    atomicMax(thr_g_q, uint32_t(lo >> 32));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------------------------
+template <bool kTf32, bool kL2>
+__global__ void __launch_bounds__(kUmThreads, 1)
+score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, const UmmaParams p) {
+  extern __shared__ unsigned char smem_dyn[];
+  // 1024-byte alignment for the 128B-swizzled stages
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+  float* thr_s = reinterpret_cast<float*>(smem + kUmSmemState);
+  uint32_t* cnt_s = reinterpret_cast<uint32_t*>(smem + kUmSmemState + kUmQMax * 4);
+  float* hn_s = reinterpret_cast<float*>(smem + kUmSmemState + kUmQMax * 8);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kUmSmemState + kUmQMax * 8 + kUmBN * 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kUmStages);
+  const uint32_t tfull0 = smem_u32(bars + 2 * kUmStages), tempty0 = smem_u32(bars + 2 * kUmStages + 2);
+  const uint32_t stage0 = smem_u32(smem);
+
+  for (int i = threadIdx.x; i < kUmQMax; i += blockDim.x) { thr_s[i] = -INFINITY; cnt_s[i] = 0u; }
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kUmStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_q)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_x)) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // contiguous range of corpus tiles for this CTA
+  const int64_t t0 = p.ntiles * blockIdx.x / gridDim.x, t1 = p.ntiles * (blockIdx.x + 1) / gridDim.x;
+  const int kelems = kTf32 ? 32 : 64;   // elements of K per stage
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0;
+      for (int64_t t = t0; t < t1; ++t) {
+        const int row = int(p.row0 + t * kUmBN);
+        for (int m = 0; m < p.mtiles; ++m) {
+          for (int k = 0; k < p.num_k; ++k) {
+            mbar_wait(empty0 + 8 * stage, phase ^ 1);
+            const uint32_t sa = stage0 + stage * kUmStageBytes;
+            mbar_expect_tx(full0 + 8 * stage, kUmStageBytes);
+            tma_load_2d(sa, &tmap_q, full0 + 8 * stage, k * kelems, m * kUmBM);
+            tma_load_2d(sa + kUmABytes, &tmap_x, full0 + 8 * stage, k * kelems, row);
+            if (++stage == kUmStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+    for (int64_t t = t0; t < t1; ++t) {
+      for (int m = 0; m < p.mtiles; ++m) {
+        mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * kUmBN;
+        for (int k = 0; k < p.num_k; ++k) {
+          mbar_wait(full0 + 8 * stage, phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t sa = stage0 + stage * kUmStageBytes;
+            const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + kUmABytes);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)   // 4 x 32 bytes of K inside the 128-byte swizzle atom
+              tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
+            tc_commit(empty0 + 8 * stage);                       // frees the smem stage when the MMAs retire
+            if (k == p.num_k - 1) tc_commit(tfull0 + 8 * acc);   // accumulator complete
+          }
+          __syncwarp();
+          if (++stage == kUmStages) { stage = 0; phase ^= 1; }
+        }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===================== epilogue: thread = query =====================
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+    const int tq = quarter * 32 + lane;           // query within the tile == TMEM lane
+    const int et = (warp - 2) * 32 + lane;        // 0..127 among epilogue threads
+    uint32_t acc = 0, acc_phase = 0;
+    for (int64_t t = t0; t < t1; ++t) {
+      const int64_t row = p.row0 + t * kUmBN;
+      const int ncols = int(p.n - row < kUmBN ? p.n - row : kUmBN);
+      if (kL2) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");          // everyone done with the previous tile's norms
+        for (int c = et; c < kUmBN; c += 128) hn_s[c] = c < ncols ? 0.5f * p.norm2[row + c] : 0.f;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+      for (int m = 0; m < p.mtiles; ++m) {
+        const int qi = m * kUmBM + tq;
+        const bool valid_q = qi < p.nq;
+        const bool warp_has_q = (m * kUmBM + quarter * 32) < p.nq;
+        float thr = -INFINITY;
+        uint32_t cnt = 0;
+        uint32_t* thr_g_q = p.thr_g + p.q0 + (valid_q ? qi : 0);
+        if (valid_q) {
+          thr = thr_s[qi];
+          cnt = cnt_s[qi];
+          uint32_t g = *reinterpret_cast<volatile uint32_t*>(thr_g_q);
+          if (g) thr = fmaxf(thr, ordered_to_f32(g));
+        }
+        uint64_t* buf = p.cand + ((size_t(blockIdx.x) * p.mt_stride + m) * p.cap) * 128 + tq;
+        mbar_wait(tfull0 + 8 * acc, acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * kUmBN;
+        if (warp_has_q) {
+          uint32_t u[32];
+          // ---- first tile of this query in this CTA: threshold by bisection over TMEM ----
+          if (t == t0 && ncols >= p.kp) {
+            float lo = INFINITY, hi = -INFINITY;
+            for (int c = 0; c < kUmBN / 32; ++c) {
+              tmem_ld32(taddr + c * 32, u);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                float s = __uint_as_float(u[i]);
+                if (kL2) s -= hn_s[c * 32 + i];
+                if (c * 32 + i < ncols) { lo = fminf(lo, s); hi = fmaxf(hi, s); }
+              }
+            }
+            uint32_t clo = uint32_t(ncols);
+            for (int it = 0; it < 24; ++it) {
+              if (!__any_sync(kFull, clo > uint32_t(p.kmax) && hi > lo)) break;
+              const float mid = 0.5f * lo + 0.5f * hi;
+              uint32_t cge = 0;
+              for (int c = 0; c < kUmBN / 32; ++c) {
+                tmem_ld32(taddr + c * 32, u);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                  float s = __uint_as_float(u[i]);
+                  if (kL2) s -= hn_s[c * 32 + i];
+                  cge += (c * 32 + i < ncols && s >= mid) ? 1u : 0u;
+                }
+              }
+              if (clo > uint32_t(p.kmax) && hi > lo) {
+                if (!(mid > lo && mid < hi)) hi = lo;                       // cannot split further (ties / rounding)
+                else if (cge >= uint32_t(p.kp)) { lo = mid; clo = cge; }    // invariant: count(s >= lo) == clo >= kp
+                else hi = mid;
+              }
+            }
+            if (valid_q && clo <= uint32_t(p.cap - 32)) {
+              thr = fmaxf(thr, lo);
+              atomicMax(thr_g_q, f32_to_ordered(lo));
+            }
+          }
+          // ---- filter + append ----
+          for (int c = 0; c < kUmBN / 32; ++c) {
+            if (c * 32 >= ncols) break;
+            const bool need = valid_q && cnt > uint32_t(p.cap - 32);
+            if (__any_sync(kFull, need)) compact_lanes(buf, cnt, thr, p.kp, p.kmax, thr_g_q, need);
+            tmem_ld32(taddr + c * 32, u);
+            if (valid_q) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                float s = __uint_as_float(u[i]);
+                if (kL2) s -= hn_s[c * 32 + i];
+                if (p.dbg && c * 32 + i < ncols) p.dbg[size_t(qi) * p.n + row + c * 32 + i] = s;
+                if (c * 32 + i < ncols && s >= thr) {
+                  buf[size_t(cnt) * 128] = make_key_max(s, uint32_t(row + c * 32 + i));
+                  ++cnt;
+                }
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+        if (valid_q) { thr_s[qi] = thr; cnt_s[qi] = cnt; }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+    // counts of this CTA's buffers
+    for (int m = 0; m < p.mtiles; ++m) {
+      const int qi = m * kUmBM + tq;
+      p.cnt[(size_t(blockIdx.x) * p.mt_stride + m) * 128 + tq] = qi < p.nq ? cnt_s[qi] : 0u;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
 struct UmmaState {
-  void release() {}
+  PFN_encodeTiled encode = nullptr;
+  void* cand = nullptr; size_t cand_bytes = 0;
+  void* cnt = nullptr; size_t cnt_bytes = 0;
+  bool attr_set[4] = {false, false, false, false};
+  void release() {
+    if (cand) cudaFree(cand);
+    if (cnt) cudaFree(cnt);
+    cand = cnt = nullptr;
+    cand_bytes = cnt_bytes = 0;
+  }
   void invalidate() {}
 };
 
@@ -15,12 +398,111 @@ struct UmmaCall {
   const void* X; int64_t n; int ld; int d; int storage;
   const void* Qh; const float* Qf; int nq; int kp;
   const float* norm2; uint32_t* thr; int sm_count;
+  float* dbg = nullptr;
 };
 
-inline bool umma_supported(int, int, int, int64_t) { return false; }
-inline int umma_launch(UmmaState&, const UmmaCall&, cudaStream_t, FinalizeParams&, int*, std::string& err) {
-  err = "tcgen05 engine not built";
-  return -5;
+inline bool umma_supported(int storage, int d, int kp, int64_t n) {
+  (void)d;
+  return storage == 1 /* bf16 */ && kp <= 256 && n > 0 && n < (int64_t(1) << 31);
+}
+
+inline int umma_make_map(UmmaState& S, CUtensorMap* map, bool f32, const void* base, uint64_t inner, uint64_t rows,
+                         uint64_t pitch_bytes, uint32_t box_rows, std::string& err) {
+  if (!S.encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || !fn) { err = "cuTensorMapEncodeTiled is not available from this driver"; return -2; }
+    S.encode = reinterpret_cast<PFN_encodeTiled>(fn);
+  }
+  cuuint64_t gdim[2] = {inner, rows};
+  cuuint64_t gstride[1] = {pitch_bytes};
+  cuuint32_t box[2] = {f32 ? 32u : 64u, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = S.encode(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { err = "cuTensorMapEncodeTiled failed with code " + std::to_string(int(r)); return -2; }
+  return 0;
+}
+
+inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
+  const bool f32 = c.storage == 0;
+  const int kelems = f32 ? 32 : 64;
+  const int num_k = (c.d + kelems - 1) / kelems;
+  const int64_t ntiles = (c.n + kUmBN - 1) / kUmBN;
+  const int grid = int(ntiles < c.sm_count ? ntiles : c.sm_count);
+  int cap = 128;
+  while (cap < 4 * c.kp) cap <<= 1;
+  const int kmax = cap / 2 - 16;
+  const int esz = f32 ? 4 : 2;
+
+  const int nlaunch = (c.nq + kUmQMax - 1) / kUmQMax;
+  const int mt_max = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
+  const size_t cand_need = size_t(nlaunch) * grid * mt_max * cap * 128 * 8;
+  const size_t cnt_need = size_t(nlaunch) * grid * mt_max * 128 * 4;
+  if (cand_need > S.cand_bytes) {
+    if (S.cand) cudaFree(S.cand);
+    S.cand = nullptr; S.cand_bytes = 0;
+    if (cudaMalloc(&S.cand, cand_need) != cudaSuccess) { cudaGetLastError(); err = "candidate scratch allocation failed"; return -3; }
+    S.cand_bytes = cand_need;
+  }
+  if (cnt_need > S.cnt_bytes) {
+    if (S.cnt) cudaFree(S.cnt);
+    S.cnt = nullptr; S.cnt_bytes = 0;
+    if (cudaMalloc(&S.cnt, cnt_need) != cudaSuccess) { cudaGetLastError(); err = "counter scratch allocation failed"; return -3; }
+    S.cnt_bytes = cnt_need;
+  }
+
+  CUtensorMap tmx;
+  int rc = umma_make_map(S, &tmx, f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * esz, kUmBN, err);
+  if (rc) return rc;
+  const int variant = (f32 ? 2 : 0) + (c.norm2 ? 1 : 0);
+  auto set_attr = [&](auto kern) -> cudaError_t {
+    if (S.attr_set[variant]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes);
+    if (e == cudaSuccess) S.attr_set[variant] = true;
+    return e;
+  };
+  for (int l = 0; l < nlaunch; ++l) {
+    const int q0 = l * kUmQMax;
+    const int nq = std::min(kUmQMax, c.nq - q0);
+    const int mtiles = (nq + kUmBM - 1) / kUmBM;
+    CUtensorMap tmq;
+    const char* qbase = f32 ? reinterpret_cast<const char*>(c.Qf) : reinterpret_cast<const char*>(c.Qh);
+    rc = umma_make_map(S, &tmq, f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), uint64_t(nq), uint64_t(c.ld) * esz, kUmBM, err);
+    if (rc) return rc;
+    UmmaParams p{};
+    p.n = c.n; p.row0 = 0; p.ntiles = ntiles; p.nq = nq; p.q0 = q0; p.mtiles = mtiles; p.mt_stride = mt_max; p.num_k = num_k;
+    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.norm2 = c.norm2; p.thr_g = c.thr;
+    p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * grid * mt_max * cap * 128;
+    p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * grid * mt_max * 128;
+    p.idesc = (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
+    p.dbg = c.dbg;
+    cudaError_t e;
+    if (f32) {
+      if (c.norm2) { e = set_attr(score_umma_kernel<true, true>); if (e == cudaSuccess) score_umma_kernel<true, true><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
+      else         { e = set_attr(score_umma_kernel<true, false>); if (e == cudaSuccess) score_umma_kernel<true, false><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
+    } else {
+      if (c.norm2) { e = set_attr(score_umma_kernel<false, true>); if (e == cudaSuccess) score_umma_kernel<false, true><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
+      else         { e = set_attr(score_umma_kernel<false, false>); if (e == cudaSuccess) score_umma_kernel<false, false><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
+    }
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("tcgen05 scoring kernel launch failed: ") + cudaGetErrorString(e); return -2; }
+    ++*launches;
+  }
+  // candidate layout for the merge kernel: slot = (launch-local) CTA, interleaved [m][entry][128]
+  fp.cand = reinterpret_cast<const uint64_t*>(S.cand);
+  fp.cnt = reinterpret_cast<const uint32_t*>(S.cnt);
+  fp.nslots = grid;
+  fp.per = cap;
+  fp.interleave = 128;
+  fp.mt_max = mt_max;
+  fp.qchunk = kUmQMax;
+  fp.slot_stride = 0;
+  fp.q_stride = 0;
+  fp.errfac = float((double(c.d) + 8.0) * 2.4e-7);   // (d+8) * 2^-22: fp32 accumulation inside the tensor core
+  return 0;
 }
 
 }  // namespace b2r

@@ -1,0 +1,202 @@
+// umma_probe.cu — bring-up / regression probe of the tcgen05 scoring kernel (not part of the product library).
+// Runs score_umma_kernel on small random problems with the dense-score debug output enabled and compares
+// every score with a host dot product; then checks that the candidate buffers contain the true top-K'.
+//   build: make -C tools      run (GPU box): timeout 120 tools/umma_probe
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../rag_tl_domainllm_optimizer_b200/csrc/score_umma.cuh"
+
+using namespace b2r;
+
+#define CK(x)                                                                                    \
+  do {                                                                                           \
+    cudaError_t e_ = (x);                                                                        \
+    if (e_ != cudaSuccess) {                                                                     \
+      printf("CUDA error %s at %s:%d: %s\n", #x, __FILE__, __LINE__, cudaGetErrorString(e_));    \
+      return 1;                                                                                  \
+    }                                                                                            \
+  } while (0)
+
+static float bf16_round(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  uint32_t lsb = (u >> 16) & 1u;
+  u += 0x7fffu + lsb;
+  u &= 0xffff0000u;
+  memcpy(&f, &u, 4);
+  return f;
+}
+static float tf32_trunc(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  u &= 0xffffe000u;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_count, unsigned seed) {
+  const int ld = (d + 63) / 64 * 64;
+  srand(seed);
+  std::vector<float> hx(size_t(n) * ld, 0.f), hq(size_t(nq) * ld, 0.f), hn2(n, 0.f);
+  for (int64_t r = 0; r < n; ++r)
+    for (int j = 0; j < d; ++j) {
+      float v = (rand() / float(RAND_MAX) - 0.5f) * 0.25f;
+      hx[r * ld + j] = f32 ? v : bf16_round(v);
+    }
+  for (int r = 0; r < nq; ++r)
+    for (int j = 0; j < d; ++j) {
+      float v = (rand() / float(RAND_MAX) - 0.5f) * 0.25f;
+      hq[size_t(r) * ld + j] = f32 ? v : bf16_round(v);
+    }
+  for (int64_t r = 0; r < n; ++r) {
+    double s = 0;
+    for (int j = 0; j < d; ++j) s += double(hx[r * ld + j]) * hx[r * ld + j];
+    hn2[r] = float(s);
+  }
+  void *dX, *dQ;
+  float *dn2, *ddbg;
+  uint32_t* dthr;
+  const size_t esz = f32 ? 4 : 2;
+  CK(cudaMalloc(&dX, size_t(n) * ld * esz));
+  CK(cudaMalloc(&dQ, size_t(nq + 256) * ld * esz));
+  CK(cudaMemset(dQ, 0, size_t(nq + 256) * ld * esz));
+  CK(cudaMalloc(&dn2, n * 4));
+  CK(cudaMalloc(&ddbg, size_t(nq) * n * 4));
+  CK(cudaMemset(ddbg, 0xff, size_t(nq) * n * 4));
+  CK(cudaMalloc(&dthr, nq * 4));
+  CK(cudaMemset(dthr, 0, nq * 4));
+  if (f32) {
+    CK(cudaMemcpy(dX, hx.data(), hx.size() * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dQ, hq.data(), hq.size() * 4, cudaMemcpyHostToDevice));
+  } else {
+    std::vector<uint16_t> bx(hx.size()), bq(hq.size());
+    for (size_t i = 0; i < hx.size(); ++i) { uint32_t u; memcpy(&u, &hx[i], 4); bx[i] = uint16_t(u >> 16); }
+    for (size_t i = 0; i < hq.size(); ++i) { uint32_t u; memcpy(&u, &hq[i], 4); bq[i] = uint16_t(u >> 16); }
+    CK(cudaMemcpy(dX, bx.data(), bx.size() * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dQ, bq.data(), bq.size() * 2, cudaMemcpyHostToDevice));
+  }
+  CK(cudaMemcpy(dn2, hn2.data(), n * 4, cudaMemcpyHostToDevice));
+
+  UmmaState S;
+  UmmaCall c{};
+  c.X = dX; c.n = n; c.ld = ld; c.d = d; c.storage = f32 ? 0 : 1;
+  c.Qh = dQ; c.Qf = reinterpret_cast<const float*>(dQ); c.nq = nq; c.kp = kp;
+  c.norm2 = l2 ? dn2 : nullptr; c.thr = dthr; c.sm_count = sm_count; c.dbg = ddbg;
+  FinalizeParams fp{};
+  int launches = 0;
+  std::string err;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaEventRecord(e0);
+  int rc = umma_launch(S, c, nullptr, fp, &launches, err);
+  cudaEventRecord(e1);
+  if (rc) { printf("  launch failed rc=%d: %s\n", rc, err.c_str()); return 1; }
+  cudaError_t se = cudaDeviceSynchronize();
+  if (se != cudaSuccess) { printf("  KERNEL FAULT: %s\n", cudaGetErrorString(se)); return 2; }
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+
+  std::vector<float> dbg(size_t(nq) * n);
+  CK(cudaMemcpy(dbg.data(), ddbg, dbg.size() * 4, cudaMemcpyDeviceToHost));
+  // dense check
+  double maxerr = 0;
+  int64_t bad = 0, unwritten = 0;
+  int shown = 0;
+  std::vector<float> ref(size_t(nq) * n);
+  for (int q = 0; q < nq; ++q)
+    for (int64_t r = 0; r < n; ++r) {
+      double s = 0;
+      for (int j = 0; j < d; ++j) {
+        float a = hq[size_t(q) * ld + j], b = hx[r * ld + j];
+        if (f32) { a = tf32_trunc(a); b = tf32_trunc(b); }
+        s += double(a) * b;
+      }
+      if (l2) s -= 0.5 * hn2[r];
+      ref[size_t(q) * n + r] = float(s);
+      float g = dbg[size_t(q) * n + r];
+      uint32_t gu;
+      memcpy(&gu, &g, 4);
+      if (gu == 0xffffffffu) { ++unwritten; continue; }
+      double e = fabs(double(g) - s);
+      maxerr = std::max(maxerr, e);
+      if (e > (f32 ? 2e-3 : 1e-4)) {
+        ++bad;
+        if (shown < 6) { printf("    mismatch q=%d row=%lld got=%g want=%g\n", q, (long long)r, g, s); ++shown; }
+      }
+    }
+  // candidate check: every true top-kp score (by the kernel's own dense scores) must be in some buffer
+  const int grid = fp.nslots, cap = fp.per, mt_max = fp.mt_max;
+  std::vector<uint64_t> cand(size_t(grid) * mt_max * cap * 128);
+  std::vector<uint32_t> cnt(size_t(grid) * mt_max * 128);
+  CK(cudaMemcpy(cand.data(), S.cand, cand.size() * 8, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(cnt.data(), S.cnt, cnt.size() * 4, cudaMemcpyDeviceToHost));
+  int64_t missing = 0, totalc = 0, maxcnt = 0;
+  for (int q = 0; q < nq && q < kUmQMax; ++q) {
+    std::vector<uint64_t> truth(n);
+    for (int64_t r = 0; r < n; ++r) truth[r] = make_key_max(dbg[size_t(q) * n + r], uint32_t(r));
+    std::sort(truth.begin(), truth.end(), [](uint64_t a, uint64_t b) { return a > b; });
+    std::vector<uint64_t> have;
+    for (int s = 0; s < grid; ++s) {
+      size_t blk = size_t(s) * mt_max + (q >> 7);
+      uint32_t cn = cnt[blk * 128 + (q & 127)];
+      maxcnt = std::max<int64_t>(maxcnt, cn);
+      for (uint32_t i = 0; i < cn && i < uint32_t(cap); ++i) have.push_back(cand[(blk * cap + i) * 128 + (q & 127)]);
+    }
+    totalc += have.size();
+    std::sort(have.begin(), have.end());
+    for (int j = 0; j < kp && j < n; ++j)
+      if (!std::binary_search(have.begin(), have.end(), truth[j])) {
+        if (missing < 4) printf("    missing q=%d rank=%d key=%016llx\n", q, j, (unsigned long long)truth[j]);
+        ++missing;
+      }
+  }
+  printf("  n=%lld nq=%d d=%d kp=%d %s %s: %.3f ms  maxerr=%.3g bad=%lld unwritten=%lld | cand/query=%.1f maxcnt=%lld cap=%d missing=%lld %s\n",
+         (long long)n, nq, d, kp, f32 ? "tf32" : "bf16", l2 ? "L2" : "IP", ms, maxerr, (long long)bad, (long long)unwritten,
+         double(totalc) / nq, (long long)maxcnt, cap, (long long)missing, (bad || unwritten || missing) ? "FAIL" : "ok");
+  S.release();
+  cudaFree(dX); cudaFree(dQ); cudaFree(dn2); cudaFree(ddbg); cudaFree(dthr);
+  return (bad || unwritten || missing) ? 3 : 0;
+}
+
+int main(int argc, char** argv) {
+  int dev = 0, sm = 148;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) { printf("no CUDA device\n"); return 1; }
+  sm = prop.multiProcessorCount;
+  printf("device: %s, %d SMs\n", prop.name, sm);
+  int fails = 0;
+  struct C { int64_t n; int nq, d, kp; bool f32, l2; };
+  const C cases[] = {
+      {256, 128, 64, 16, false, false},     // one tile, one K step
+      {256, 128, 128, 16, false, false},    // two K steps
+      {512, 128, 768, 16, false, false},
+      {300, 5, 64, 16, false, false},       // ragged rows and queries
+      {4096, 70, 384, 16, false, false},
+      {20000, 200, 768, 16, false, false},  // 2 m-tiles
+      {20000, 33, 768, 16, false, true},    // L2
+      {100000, 8, 768, 106, false, false},  // k=100 sized buffers
+      {20000, 300, 100, 16, false, false},  // d not a multiple of 64
+      {256, 128, 32, 16, true, false},      // tf32, one K step
+      {4096, 70, 384, 16, true, false},
+      {20000, 33, 768, 16, true, true},
+  };
+  int only = argc > 1 ? atoi(argv[1]) : -1;
+  int idx = 0;
+  for (const C& c : cases) {
+    if (only >= 0 && idx++ != only) continue;
+    int rc = run_case(c.n, c.nq, c.d, c.kp, c.f32, c.l2, sm, 1234u + unsigned(c.n));
+    if (rc == 2) { printf("aborting after a kernel fault\n"); return 2; }
+    fails += rc != 0;
+  }
+  printf("%d failing case(s)\n", fails);
+  return fails ? 1 : 0;
+}
