@@ -253,7 +253,8 @@ def main():
         t0 = time.perf_counter()
         for _ in range(steps):
             D, I = sidx.search(q_host, args.k)
-            D_h, I_h = D.cpu(), I.cpu()     # device -> host read of the step's result
+            D_h = D.cpu() if hasattr(D, "cpu") else torch.from_numpy(D)     # device -> host read of the step's result
+            I_h = I.cpu() if hasattr(I, "cpu") else torch.from_numpy(I)     # (host-buffer callers get it from the C ABI)
         barrier()
         return max_over_ranks((time.perf_counter() - t0) * 1e3) / steps, D_h, I_h
 
@@ -264,7 +265,7 @@ def main():
     ms_step, score_ms = timed_device(q, args.steps, args.warmup)
     clocks = sampler.stop()
     st = sidx.local.last_stats()
-    launches_per_step = st["launches"] + (1 if True else 0)   # + the merge kernel of the gathered lists
+    launches_per_step = st["launches"] + (1 if world > 1 else 0)   # + the merge kernel of the gathered lists
     qps = args.batch / (ms_step * 1e-3)
 
     q_pinned = torch.empty((args.batch, DIM), dtype=torch.float32, pin_memory=True)

@@ -1,33 +1,38 @@
 // finalize.cuh — kernel (c): block/grid-level top-k merge, fused with the exact re-scoring.
 //
-// One CTA per query:
-//   1. streams the query's candidate keys from every slot (one slot per scoring CTA), drops
-//      empties and everything below the final grid-wide threshold, and keeps the best K' with
-//      shared-memory bitonic rounds (no candidate list is ever written back to HBM);
+// One CTA (1024 threads) per query:
+//   1. gathers the query's candidate keys from every slot (one slot per scoring CTA) — only the valid entries,
+//      located through a prefix sum of the per-slot counts — drops everything below the final grid-wide
+//      threshold and keeps the best K' with shared-memory bitonic sorts sized to what survived
+//      (no candidate list is ever written back to HBM);
 //   2. re-scores the K' survivors with the DOT64 arithmetic that defines the returned score
 //      (one warp per candidate row, fp64 fixed-order reduction of the stored row);
 //   3. sorts them by (fp32 score best-first, id ascending) and writes D/I (or packed keys for
 //      the cross-GPU all-gather);
 //   4. proves completeness: if fl32(a_min + E) is strictly worse than the k-th returned score,
 //      no row that the scoring pass filtered out can belong to the top-k.
-// The same kernel body merges the all-gathered [G,nq,k] packed lists (merge_packed_kernel).
+// The same gather merges the all-gathered [G,nq,k] packed lists (merge_packed_kernel) and selects the seed
+// thresholds of the tcgen05 engine (seed_select_kernel in score_umma.cuh).
 #pragma once
 #include <float.h>
 #include "common.cuh"
 
 namespace b2r {
 
+constexpr int kFinThreads = 1024;
+constexpr int kFinMaxSlots = 1024;
+
 struct FinalizeParams {
   const uint64_t* cand;    // candidate keys
   int64_t slot_stride;     // elements between consecutive slots
   int64_t q_stride;        // elements between consecutive queries inside a slot
   int nslots;
-  int per;                 // entries to scan per (slot, query)
-  const uint32_t* cnt;     // optional valid-entry counts; nullptr = scan `per`, skip zeros
+  int per;                 // capacity (entries) of one (slot, query) list
+  const uint32_t* cnt;     // optional valid-entry counts; nullptr = all `per` entries, zeros skipped
   int interleave;          // 0: cand[slot*slot_stride + q*q_stride + i], cnt[slot*nq + q]
                            // 128 (tcgen05 engine): queries are grouped in launches of `qchunk` and tiles of 128;
-                           //   cand[(((l*nslots + slot)*mt_max + m)*per + i)*128 + t], cnt[((l*nslots + slot)*mt_max + m)*128 + t]
-  int mt_max, qchunk;
+                           //   cand[(((l*slot_total + slot)*mt_max + m)*per + i)*128 + t], cnt[((l*slot_total + slot)*mt_max + m)*128 + t]
+  int mt_max, qchunk, slot_total;   // slot_total: slots per query chunk in the layout (>= nslots scanned)
   const uint32_t* thr;     // optional ordered-float thresholds [nq] (0 = none)
   int nq, kp, k, sortn;
   const void* X; int ld; int d; int storage;
@@ -38,68 +43,92 @@ struct FinalizeParams {
   unsigned long long* stats;  // [0] unverified queries, [1] candidates seen
 };
 
-// Keeps the best `keep` of a stream of keys in s[0..keep) (sorted descending), using s[0..sortn).
-// fetch(e) returns the e-th raw key or 0.  Returns min(#non-zero keys, keep).  Block-collective.
-template <typename Fetch>
-__device__ __forceinline__ int stream_topk(uint64_t* s, int sortn, int keep, int64_t total, Fetch fetch,
-                                           int* fill_s, unsigned long long* seen) {
-  const int tid = threadIdx.x, nt = blockDim.x;
-  for (int i = tid; i < sortn; i += nt) s[i] = 0ull;
-  if (tid == 0) *fill_s = 0;
+// Gathers the keys of `nslots` lists (list s holds cnt_of(s) keys key_of(s, i)), drops zero keys and keys whose
+// score half is below thr_hi, and leaves the best `keep` in s[0..keep) sorted descending (s has sortn entries,
+// sortn >= keep + blockDim).  Returns min(#kept keys, keep).  Block-collective; off_s is [kFinMaxSlots + 1] ints.
+template <typename CntF, typename KeyF>
+__device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int nslots, CntF cnt_of, KeyF key_of,
+                                           uint32_t thr_hi, int* off_s, int* fill_s, unsigned long long* seen) {
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
+  for (int sl = tid; sl < nslots; sl += nt) off_s[sl + 1] = cnt_of(sl);
+  if (tid == 0) { off_s[0] = 0; *fill_s = 0; }
   __syncthreads();
-  unsigned long long mine = 0;
-  int ub = 0;  // uniform upper bound of *fill_s, tracked in registers so the branch never diverges
-  for (int64_t base = 0; base < total; base += nt) {
-    if (ub + nt > sortn) {
-      block_bitonic_desc(s, sortn);
-      if (tid == 0) *fill_s = min(*fill_s, keep);
-      for (int i = keep + tid; i < sortn; i += nt) s[i] = 0ull;
-      __syncthreads();
-      ub = keep;
+  if (tid < 32) {   // inclusive prefix sum of off_s[1..nslots] by one warp
+    const int per_lane = (nslots + 31) / 32;
+    const int b = lane * per_lane, e = min(nslots, b + per_lane);
+    int sum = 0;
+    for (int i = b; i < e; ++i) sum += off_s[i + 1];
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int v = __shfl_up_sync(kFull, incl, o);
+      if (lane >= o) incl += v;
     }
-    ub += nt;
-    int64_t e = base + tid;
-    uint64_t key = e < total ? fetch(e) : 0ull;
-    if (key) {
-      int pos = atomicAdd(fill_s, 1);
-      s[pos] = key;
-      ++mine;
-    }
-    __syncthreads();
+    int run = incl - sum;
+    for (int i = b; i < e; ++i) { run += off_s[i + 1]; off_s[i + 1] = run; }
   }
-  block_bitonic_desc(s, sortn);
-  if (seen && mine) atomicAdd(seen, mine);
-  int got = min(*fill_s, keep);
   __syncthreads();
-  return got;
+  const int total = off_s[nslots];
+  int fill = 0;   // uniform copy of *fill_s
+  unsigned long long mine = 0;
+  for (int base = 0; base < total; base += nt) {
+    if (fill + nt > sortn) {   // make room: keep the best `keep` so far
+      for (int i = fill + tid; i < sortn; i += nt) s[i] = 0ull;
+      __syncthreads();
+      block_bitonic_desc(s, sortn);
+      fill = min(fill, keep);
+      if (tid == 0) *fill_s = fill;
+      __syncthreads();
+    }
+    const int e = base + tid;
+    bool pass = false;
+    if (e < total) {
+      int lo = 0, hi = nslots;            // largest slot with off_s[slot] <= e
+      while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (off_s[mid] <= e) lo = mid; else hi = mid;
+      }
+      const uint64_t key = key_of(lo, e - off_s[lo]);
+      pass = key != 0ull && uint32_t(key >> 32) >= thr_hi;
+      if (pass) {
+        s[atomicAdd(fill_s, 1)] = key;
+        ++mine;
+      }
+    }
+    fill += __syncthreads_count(pass);
+  }
+  int nsort = 2;
+  while (nsort < fill) nsort <<= 1;
+  for (int i = fill + tid; i < nsort; i += nt) s[i] = 0ull;
+  __syncthreads();
+  block_bitonic_desc(s, nsort);
+  if (seen && mine) atomicAdd(seen, mine);
+  return min(fill, keep);
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) finalize_kernel(FinalizeParams p) {
+__global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* s = reinterpret_cast<uint64_t*>(smem_raw);   // [sortn]
   const int kp2 = next_pow2(p.kp);
   uint64_t* s2 = s + p.sortn;                             // [kp2]
   __shared__ int fill_s;
+  __shared__ int off_s[kFinMaxSlots + 1];
   const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
   const T* X = reinterpret_cast<const T*>(p.X);
 
   const uint32_t thrq = p.thr ? p.thr[q] : 0u;
   const int ql = p.interleave ? q % p.qchunk : 0, lq = p.interleave ? q / p.qchunk : 0;
-  auto fetch = [&](int64_t e) -> uint64_t {
-    int slot = int(e / p.per), i = int(e % p.per);
-    uint64_t key;
-    if (p.interleave) {
-      const size_t blk = (size_t(lq) * p.nslots + slot) * p.mt_max + (ql >> 7);
-      if (uint32_t(i) >= p.cnt[blk * 128 + (ql & 127)]) return 0ull;
-      key = p.cand[(blk * p.per + i) * 128 + (ql & 127)];
-    } else {
-      if (p.cnt && uint32_t(i) >= p.cnt[int64_t(slot) * p.nq + q]) return 0ull;
-      key = p.cand[slot * p.slot_stride + q * p.q_stride + i];
-    }
-    return (uint32_t(key >> 32) >= thrq) ? key : 0ull;
+  auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
+  auto cnt_of = [&](int slot) -> int {
+    if (p.interleave) return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per)));
+    return p.cnt ? int(min(p.cnt[int64_t(slot) * p.nq + q], uint32_t(p.per))) : p.per;
   };
-  const int ncand = stream_topk(s, p.sortn, p.kp, int64_t(p.nslots) * p.per, fetch, &fill_s, p.stats ? p.stats + 1 : nullptr);
+  auto key_of = [&](int slot, int i) -> uint64_t {
+    if (p.interleave) return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)];
+    return p.cand[slot * p.slot_stride + q * p.q_stride + i];
+  };
+  const int ncand = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, thrq, off_s, &fill_s, p.stats ? p.stats + 1 : nullptr);
 
   // exact re-scoring of the survivors
   const float* qrow = p.Q + int64_t(q) * p.ldq;
@@ -163,12 +192,11 @@ __global__ void __launch_bounds__(256) merge_packed_kernel(const uint64_t* __res
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* s = reinterpret_cast<uint64_t*>(smem_raw);
   __shared__ int fill_s;
+  __shared__ int off_s[kFinMaxSlots + 1];
   const int q = blockIdx.x;
-  auto fetch = [&](int64_t e) -> uint64_t {
-    int g = int(e / k), i = int(e % k);
-    return packed[(int64_t(g) * nq + q) * k + i];
-  };
-  const int got = stream_topk(s, sortn, k, int64_t(G) * k, fetch, &fill_s, nullptr);
+  auto cnt_of = [&](int) -> int { return k; };
+  auto key_of = [&](int g, int i) -> uint64_t { return packed[(int64_t(g) * nq + q) * k + i]; };
+  const int got = gather_topk(s, sortn, k, G, cnt_of, key_of, 0u, off_s, &fill_s, nullptr);
   for (int j = threadIdx.x; j < k; j += blockDim.x) {
     const bool have = j < got;
     uint64_t key = have ? s[j] : 0ull;

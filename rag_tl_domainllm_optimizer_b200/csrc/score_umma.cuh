@@ -25,7 +25,9 @@
 // Algorithmic flops: 2 * nq * rows * d.
 #pragma once
 #include <cuda.h>
+#include <algorithm>
 #include <string>
+#include <vector>
 #include "common.cuh"
 #include "finalize.cuh"
 
@@ -58,6 +60,8 @@ struct UmmaParams {
   uint64_t* cand;     // [grid][mtiles][cap][128]
   uint32_t* cnt;      // [grid][mtiles*128]
   uint32_t idesc;
+  int slot_base;      // first scratch slot of this launch (seed launch: 0, main launch: #seed CTAs)
+  int bisect_first;   // seed launch: find the first tile's threshold by bisection over TMEM
   float* dbg;         // optional [nq][n] dense scores (probe only)
 };
 
@@ -156,7 +160,7 @@ __device__ __forceinline__ void compact_lanes(uint64_t* buf, uint32_t& cnt, floa
     const uint64_t mid = lo + ((hi - lo) >> 1) + 1;   // lo < mid <= hi
     uint32_t c = 0;
     const uint32_t nn = act ? n : 0u;
-#pragma unroll 4
+#pragma unroll 8
     for (uint32_t e = 0; e < nn; ++e) c += (buf[size_t(e) * 128] >= mid) ? 1u : 0u;
     if (act) {
       if (c >= uint32_t(kp)) { lo = mid; clo = c; } else { hi = mid - 1; }
@@ -287,14 +291,14 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           uint32_t g = *reinterpret_cast<volatile uint32_t*>(thr_g_q);
           if (g) thr = fmaxf(thr, ordered_to_f32(g));
         }
-        uint64_t* buf = p.cand + ((size_t(blockIdx.x) * p.mt_stride + m) * p.cap) * 128 + tq;
+        uint64_t* buf = p.cand + ((size_t(p.slot_base + blockIdx.x) * p.mt_stride + m) * p.cap) * 128 + tq;
         mbar_wait(tfull0 + 8 * acc, acc_phase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * kUmBN;
         if (warp_has_q) {
           uint32_t u[32];
           // ---- first tile of this query in this CTA: threshold by bisection over TMEM ----
-          if (t == t0 && ncols >= p.kp) {
+          if (p.bisect_first && t == t0 && ncols >= p.kp) {
             float lo = INFINITY, hi = -INFINITY;
             for (int c = 0; c < kUmBN / 32; ++c) {
               tmem_ld32(taddr + c * 32, u);
@@ -361,7 +365,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // counts of this CTA's buffers
     for (int m = 0; m < p.mtiles; ++m) {
       const int qi = m * kUmBM + tq;
-      p.cnt[(size_t(blockIdx.x) * p.mt_stride + m) * 128 + tq] = qi < p.nq ? cnt_s[qi] : 0u;
+      p.cnt[(size_t(p.slot_base + blockIdx.x) * p.mt_stride + m) * 128 + tq] = qi < p.nq ? cnt_s[qi] : 0u;
     }
   }
 
@@ -384,7 +388,7 @@ struct UmmaState {
   PFN_encodeTiled encode = nullptr;
   void* cand = nullptr; size_t cand_bytes = 0;
   void* cnt = nullptr; size_t cnt_bytes = 0;
-  bool attr_set[4] = {false, false, false, false};
+  bool attr_set[5] = {false, false, false, false, false};
   void release() {
     if (cand) cudaFree(cand);
     if (cnt) cudaFree(cnt);
@@ -426,12 +430,34 @@ inline int umma_make_map(UmmaState& S, CUtensorMap* map, bool f32, const void* b
   return 0;
 }
 
+// Seed thresholds: K'-th best candidate of the seed launch's slots -> thr_g[q] (a valid lower bound of the final
+// K'-th best, since it is the K'-th best score of a real subset of the rows).  One CTA per query.
+__global__ void __launch_bounds__(kFinThreads) seed_select_kernel(FinalizeParams p, uint32_t* thr_g) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* s = reinterpret_cast<uint64_t*>(smem_raw);
+  __shared__ int fill_s;
+  __shared__ int off_s[kFinMaxSlots + 1];
+  const int q = blockIdx.x;
+  const int ql = q % p.qchunk, lq = q / p.qchunk;
+  auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
+  auto cnt_of = [&](int slot) -> int { return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per))); };
+  auto key_of = [&](int slot, int i) -> uint64_t { return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)]; };
+  const int got = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, 0u, off_s, &fill_s, nullptr);
+  if (threadIdx.x == 0 && got == p.kp) atomicMax(thr_g + q, uint32_t(s[p.kp - 1] >> 32));
+}
+
 inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
   const bool f32 = c.storage == 0;
   const int kelems = f32 ? 32 : 64;
   const int num_k = (c.d + kelems - 1) / kelems;
   const int64_t ntiles = (c.n + kUmBN - 1) / kUmBN;
-  const int grid = int(ntiles < c.sm_count ? ntiles : c.sm_count);
+  // seed launch: one tile per CTA over the first rows; main launch: everything after them
+  // (seed size: enough rows for a sharp threshold, few enough CTAs for a cheap selection)
+  const int64_t seed_want = std::max<int64_t>(32, std::min<int64_t>(c.sm_count, ntiles / 64));
+  const int grid_seed = int(std::min<int64_t>(ntiles, seed_want));
+  const int64_t tiles_main = ntiles - grid_seed;
+  const int grid_main = int(tiles_main < c.sm_count ? tiles_main : c.sm_count);
+  const int slots = grid_seed + grid_main;
   int cap = 128;
   while (cap < 4 * c.kp) cap <<= 1;
   const int kmax = cap / 2 - 16;
@@ -439,8 +465,8 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
 
   const int nlaunch = (c.nq + kUmQMax - 1) / kUmQMax;
   const int mt_max = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
-  const size_t cand_need = size_t(nlaunch) * grid * mt_max * cap * 128 * 8;
-  const size_t cnt_need = size_t(nlaunch) * grid * mt_max * 128 * 4;
+  const size_t cand_need = size_t(nlaunch) * slots * mt_max * cap * 128 * 8;
+  const size_t cnt_need = size_t(nlaunch) * slots * mt_max * 128 * 4;
   if (cand_need > S.cand_bytes) {
     if (S.cand) cudaFree(S.cand);
     S.cand = nullptr; S.cand_bytes = 0;
@@ -458,43 +484,28 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
   int rc = umma_make_map(S, &tmx, f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * esz, kUmBN, err);
   if (rc) return rc;
   const int variant = (f32 ? 2 : 0) + (c.norm2 ? 1 : 0);
-  auto set_attr = [&](auto kern) -> cudaError_t {
-    if (S.attr_set[variant]) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes);
-    if (e == cudaSuccess) S.attr_set[variant] = true;
+  auto launch = [&](int grid, const CUtensorMap& tmq, const UmmaParams& p) -> cudaError_t {
+    cudaError_t e = cudaSuccess;
+#define B2R_UM_LAUNCH(TF, L2)                                                                                      \
+  do {                                                                                                             \
+    if (!S.attr_set[variant]) {                                                                                    \
+      e = cudaFuncSetAttribute(score_umma_kernel<TF, L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes); \
+      if (e == cudaSuccess) S.attr_set[variant] = true;                                                            \
+    }                                                                                                              \
+    if (e == cudaSuccess) score_umma_kernel<TF, L2><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p);          \
+  } while (0)
+    if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true); else B2R_UM_LAUNCH(true, false); }
+    else     { if (c.norm2) B2R_UM_LAUNCH(false, true); else B2R_UM_LAUNCH(false, false); }
+#undef B2R_UM_LAUNCH
+    if (e == cudaSuccess) e = cudaGetLastError();
     return e;
   };
-  for (int l = 0; l < nlaunch; ++l) {
-    const int q0 = l * kUmQMax;
-    const int nq = std::min(kUmQMax, c.nq - q0);
-    const int mtiles = (nq + kUmBM - 1) / kUmBM;
-    CUtensorMap tmq;
-    const char* qbase = f32 ? reinterpret_cast<const char*>(c.Qf) : reinterpret_cast<const char*>(c.Qh);
-    rc = umma_make_map(S, &tmq, f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), uint64_t(nq), uint64_t(c.ld) * esz, kUmBM, err);
-    if (rc) return rc;
-    UmmaParams p{};
-    p.n = c.n; p.row0 = 0; p.ntiles = ntiles; p.nq = nq; p.q0 = q0; p.mtiles = mtiles; p.mt_stride = mt_max; p.num_k = num_k;
-    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.norm2 = c.norm2; p.thr_g = c.thr;
-    p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * grid * mt_max * cap * 128;
-    p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * grid * mt_max * 128;
-    p.idesc = (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
-    p.dbg = c.dbg;
-    cudaError_t e;
-    if (f32) {
-      if (c.norm2) { e = set_attr(score_umma_kernel<true, true>); if (e == cudaSuccess) score_umma_kernel<true, true><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
-      else         { e = set_attr(score_umma_kernel<true, false>); if (e == cudaSuccess) score_umma_kernel<true, false><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
-    } else {
-      if (c.norm2) { e = set_attr(score_umma_kernel<false, true>); if (e == cudaSuccess) score_umma_kernel<false, true><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
-      else         { e = set_attr(score_umma_kernel<false, false>); if (e == cudaSuccess) score_umma_kernel<false, false><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p); }
-    }
-    if (e == cudaSuccess) e = cudaGetLastError();
-    if (e != cudaSuccess) { err = std::string("tcgen05 scoring kernel launch failed: ") + cudaGetErrorString(e); return -2; }
-    ++*launches;
-  }
-  // candidate layout for the merge kernel: slot = (launch-local) CTA, interleaved [m][entry][128]
+
+  // layout of the scratch for the merge kernel: slot = CTA of either launch, interleaved [m][entry][128]
   fp.cand = reinterpret_cast<const uint64_t*>(S.cand);
   fp.cnt = reinterpret_cast<const uint32_t*>(S.cnt);
-  fp.nslots = grid;
+  fp.nslots = slots;
+  fp.slot_total = slots;
   fp.per = cap;
   fp.interleave = 128;
   fp.mt_max = mt_max;
@@ -502,6 +513,52 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
   fp.slot_stride = 0;
   fp.q_stride = 0;
   fp.errfac = float((double(c.d) + 8.0) * 2.4e-7);   // (d+8) * 2^-22: fp32 accumulation inside the tensor core
+
+  std::vector<CUtensorMap> tmq(nlaunch);
+  std::vector<UmmaParams> pp(nlaunch);
+  for (int l = 0; l < nlaunch; ++l) {
+    const int q0 = l * kUmQMax;
+    const int nq = std::min(kUmQMax, c.nq - q0);
+    const char* qbase = f32 ? reinterpret_cast<const char*>(c.Qf) : reinterpret_cast<const char*>(c.Qh);
+    rc = umma_make_map(S, &tmq[l], f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), uint64_t(nq), uint64_t(c.ld) * esz, kUmBM, err);
+    if (rc) return rc;
+    UmmaParams& p = pp[l];
+    p = UmmaParams{};
+    p.n = c.n; p.nq = nq; p.q0 = q0; p.mtiles = (nq + kUmBM - 1) / kUmBM; p.mt_stride = mt_max; p.num_k = num_k;
+    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.norm2 = c.norm2; p.thr_g = c.thr;
+    p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * slots * mt_max * cap * 128;
+    p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * slots * mt_max * 128;
+    p.idesc = (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
+    p.dbg = c.dbg;
+    // seed launch
+    p.row0 = 0; p.ntiles = grid_seed; p.slot_base = 0; p.bisect_first = 1;
+    cudaError_t e = launch(grid_seed, tmq[l], p);
+    if (e != cudaSuccess) { err = std::string("tcgen05 seed launch failed: ") + cudaGetErrorString(e); return -2; }
+    ++*launches;
+  }
+  if (grid_main > 0) {
+    // thresholds from the seed slots, then the main launch over the remaining rows
+    FinalizeParams sp = fp;
+    sp.nslots = grid_seed;
+    sp.kp = c.kp;
+    sp.sortn = 8192;
+    if (!S.attr_set[4]) {
+      cudaError_t ea = cudaFuncSetAttribute(seed_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8);
+      if (ea != cudaSuccess) { err = std::string("seed_select attribute failed: ") + cudaGetErrorString(ea); return -2; }
+      S.attr_set[4] = true;
+    }
+    seed_select_kernel<<<c.nq, kFinThreads, size_t(sp.sortn) * 8, st>>>(sp, c.thr);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("seed_select launch failed: ") + cudaGetErrorString(e); return -2; }
+    ++*launches;
+    for (int l = 0; l < nlaunch; ++l) {
+      UmmaParams& p = pp[l];
+      p.row0 = int64_t(grid_seed) * kUmBN; p.ntiles = tiles_main; p.slot_base = grid_seed; p.bisect_first = 0;
+      e = launch(grid_main, tmq[l], p);
+      if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
+      ++*launches;
+    }
+  }
   return 0;
 }
 

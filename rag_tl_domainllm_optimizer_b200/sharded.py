@@ -47,6 +47,8 @@ class ShardedIndexFlat:
 
     def search(self, x, k: int):
         import torch
+        if self.world == 1 and self.row_offset == 0 and hasattr(self.local, "search"):
+            return self.local.search(x, k)                                # one shard: nothing to gather or merge
         packed = self.local.search_packed(x, k, self.row_offset)          # [nq,k] on this GPU
         if self.world == 1:
             return self._merge(packed.unsqueeze(0), self.metric_type)
