@@ -188,6 +188,23 @@ int b2r_normalize_l2(int64_t n, int64_t d, float* x, int device, void* stream);
 int b2r_cosine_rows(int64_t n, int64_t m, int64_t d, const float* resp, const float* docs,
                     float* cos, float* maxcos, int device, void* stream);
 
+/* Largest n b2r_cosine_rows_noalloc accepts (entries of its fixed device scratch). */
+#define B2R_NOALLOC_MAX_SAMPLES 65536
+
+/* b2r_cosine_rows for callers that must not allocate.  No counterpart in the reference.
+ * Meant for the reward step inside a training or serving loop whose framework owns all free device
+ * memory (a raw cudaMalloc there can fail, and cudaMalloc/cudaFree stall every stream of the device),
+ * and for loops that forbid allocation after warm-up.  Same arithmetic and outputs as b2r_cosine_rows,
+ * but: DEVICE pointers only (resp [n,d], docs [n,m,d], cos [n,m] or NULL, maxcos [n]); the work is only
+ * enqueued on `stream`; n <= B2R_NOALLOC_MAX_SAMPLES, larger n is refused with B2R_ERR_LIMIT.
+ * Its scratch is a fixed 256 KiB array that lives on every GPU that has loaded the library until the
+ * process exits; the call performs no cudaMalloc / cudaFree or other allocating routine.
+ * The first call on each device looks up that array's device address; make that first call outside
+ * any stream capture.  All calls on a device share the array (each call clears the part it uses), so
+ * two calls whose GPU work overlaps — different streams, or different threads — race: serialise them. */
+int b2r_cosine_rows_noalloc(int64_t n, int64_t m, int64_t d, const float* resp, const float* docs,
+                            float* cos, float* maxcos, int device, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

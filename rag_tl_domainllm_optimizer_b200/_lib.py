@@ -27,6 +27,7 @@ EXPORTS = [
     "b2r_index_reserve", "b2r_index_reset", "b2r_index_ntotal", "b2r_index_reconstruct", "b2r_index_search",
     "b2r_index_search_ex", "b2r_index_search_packed", "b2r_merge_packed", "b2r_index_set_engine",
     "b2r_index_set_pad", "b2r_index_last_stats", "b2r_index_last_score_ms", "b2r_index_score_time", "b2r_normalize_l2", "b2r_cosine_rows",
+    "b2r_cosine_rows_noalloc",
 ]
 
 
@@ -86,6 +87,7 @@ def lib() -> ctypes.CDLL:
     L.b2r_index_score_time.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64)]
     L.b2r_normalize_l2.argtypes = [i64, i64, vp, i32, vp]
     L.b2r_cosine_rows.argtypes = [i64, i64, i64, vp, vp, vp, vp, i32, vp]
+    L.b2r_cosine_rows_noalloc.argtypes = [i64, i64, i64, vp, vp, vp, vp, i32, vp]
     _lib = L
     return L
 

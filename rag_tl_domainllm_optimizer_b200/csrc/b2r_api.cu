@@ -668,3 +668,64 @@ extern "C" int b2r_cosine_rows(int64_t n, int64_t m, int64_t d, const float* res
   if (e != cudaSuccess) return fail(B2R_ERR_CUDA, "cosine_rows failed: %s", cudaGetErrorString(e));
   return B2R_OK;
 }
+
+// --------------------------------------------------------------------------------------
+// allocation-free reward cosine
+// --------------------------------------------------------------------------------------
+// Who needs this: the reward scoring sits inside the PPO batch loop (reference :297-302), next to a policy
+// whose framework has usually taken all free device memory into its own caching pool.  In such a process a
+// raw cudaMalloc can fail although the pool has room, and cudaMalloc / cudaFree also serialise the whole
+// device, stalling the policy's own streams.  Serving loops that forbid allocation after warm-up have the
+// same constraint.  b2r_cosine_rows allocates a small workspace per call; this variant does not: its only
+// scratch (one ordered-float running maximum per sample) is the fixed array below, resident on every GPU
+// that loads the library until the process exits (256 KiB).
+static __device__ __align__(256) uint32_t g_noalloc_maxord[B2R_NOALLOC_MAX_SAMPLES];
+
+// g_noalloc_maxord is a host-side stand-in in host code, not a device address: the device address is looked
+// up once per device (with that device current) and cached here.
+static std::mutex g_noalloc_mu;
+static uint32_t* g_noalloc_dev_ptr[64] = {};
+
+extern "C" int b2r_cosine_rows_noalloc(int64_t n, int64_t m, int64_t d, const float* resp, const float* docs,
+                                       float* cosout, float* maxcos, int device, void* stream) {
+  if (n < 0 || m < 0 || d <= 0) return fail(B2R_ERR_ARG, "bad shape n=%lld m=%lld d=%lld", (long long)n, (long long)m, (long long)d);
+  if (n > B2R_NOALLOC_MAX_SAMPLES)
+    return fail(B2R_ERR_LIMIT, "n=%lld exceeds B2R_NOALLOC_MAX_SAMPLES=%d: the fixed scratch holds one entry per sample; "
+                "split the batch or use b2r_cosine_rows", (long long)n, B2R_NOALLOC_MAX_SAMPLES);
+  if (n == 0) return B2R_OK;
+  if (!resp || !maxcos || (m > 0 && !docs)) return fail(B2R_ERR_ARG, "null argument");
+  const int ndev = b2r_device_count();
+  if (ndev <= 0) return fail(B2R_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
+  if (device < 0 || device >= ndev || device >= 64) return fail(B2R_ERR_ARG, "device %d out of range", device);
+  if (!is_device_ptr(resp) || !is_device_ptr(maxcos) || (m > 0 && !is_device_ptr(docs)) || (cosout && !is_device_ptr(cosout)))
+    return fail(B2R_ERR_ARG, "b2r_cosine_rows_noalloc takes device pointers only (staging host buffers would need an allocation)");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  uint32_t* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_dev_ptr[device]) {   // first call on this device: resolve the symbol's device address
+      void* p = nullptr;
+      cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_maxord);
+      if (e != cudaSuccess || !p) {
+        cudaGetLastError();
+        return fail(B2R_ERR_CUDA, "cudaGetSymbolAddress(noalloc scratch) failed on device %d: %s", device, cudaGetErrorString(e));
+      }
+      g_noalloc_dev_ptr[device] = static_cast<uint32_t*>(p);
+    }
+    scratch = g_noalloc_dev_ptr[device];
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // the array keeps the previous call's maxima: the entries this call uses must start at "no value" (0)
+  CU_TRY(cudaMemsetAsync(scratch, 0, size_t(n) * sizeof(uint32_t), st));
+  if (m > 0) {
+    int sm = 148;
+    cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device);
+    const int blocks = int(std::min<int64_t>((n * m + 7) / 8, int64_t(sm) * 16));
+    cosine_rows_kernel<<<blocks, 256, 0, st>>>(resp, docs, n, m, int(d), cosout, scratch);
+    CU_TRY(cudaGetLastError());
+  }
+  finish_maxcos_kernel<<<int((n + 255) / 256), 256, 0, st>>>(scratch, n, maxcos);
+  CU_TRY(cudaGetLastError());
+  return B2R_OK;
+}
