@@ -74,6 +74,9 @@ typedef struct b2r_search_stats {
   int64_t candidates;     /* candidate entries that reached the merge kernel            */
   int32_t engine;         /* B2R_ENGINE_FMA or B2R_ENGINE_UMMA actually used            */
   int32_t launches;       /* kernels launched by the call                               */
+  int32_t fallback;       /* 1 if an exact-mode tensor-core search could not be proven  */
+                          /* and the call was repeated on the fp32 FMA engine           */
+  int32_t reserved;
 } b2r_search_stats;
 
 /* Library / device ------------------------------------------------------------------ */

@@ -136,6 +136,8 @@ struct b2r_index {
   float* maxnorm2 = nullptr;  // device scalar: largest stored squared norm
   int sm_count = 148;
   int engine = B2R_ENGINE_AUTO, pad = 6;
+  bool verify = true;                  // exact mode: re-run unproven tensor-core searches on the FMA engine
+  unsigned long long* host_flag = nullptr;   // pinned, for that check
   // per-search workspace
   DevBuf qf, qh, qn2, thr, cand, cnt, stats, stage_q, stage_d, stage_i, stage_x, misc;
   static constexpr int kEvPool = 256;           // scoring-kernel timers: one event pair per recent search
@@ -172,6 +174,7 @@ extern "C" int b2r_index_create(b2r_index** out, int64_t d, int metric, int stor
   idx->sm_count = prop.multiProcessorCount;
   cudaError_t e = cudaMalloc(&idx->maxnorm2, sizeof(float));
   if (e == cudaSuccess) e = cudaMemset(idx->maxnorm2, 0, sizeof(float));
+  if (e == cudaSuccess) e = cudaMallocHost(&idx->host_flag, sizeof(unsigned long long));
   for (int i = 0; i < b2r_index::kEvPool && e == cudaSuccess; ++i) {
     e = cudaEventCreate(&idx->ev0[i]);
     if (e == cudaSuccess) e = cudaEventCreate(&idx->ev1[i]);
@@ -191,6 +194,7 @@ extern "C" void b2r_index_free(b2r_index* idx) {
   if (idx->X) cudaFree(idx->X);
   if (idx->norm2) cudaFree(idx->norm2);
   if (idx->maxnorm2) cudaFree(idx->maxnorm2);
+  if (idx->host_flag) cudaFreeHost(idx->host_flag);
   DevBuf* bufs[] = {&idx->qf, &idx->qh, &idx->qn2, &idx->thr, &idx->cand, &idx->cnt, &idx->stats,
                     &idx->stage_q, &idx->stage_d, &idx->stage_i, &idx->stage_x, &idx->misc};
   for (DevBuf* b : bufs) b->release();
@@ -388,11 +392,21 @@ static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, Final
 }
 
 static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t k, int normalize_queries,
-                         int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st) {
-  const int kp = int(std::min<int64_t>(k + idx->pad, 2048));
+                         int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st, bool force_fma) {
+  // engine and K': the TF32 tensor-core pass truncates both operands to 10 mantissa bits, so it keeps a wider
+  // candidate list (pad >= 22) for the completeness proof to go through; FMA and bf16 (exact products) keep pad.
+  bool use_umma = false;
+  int kp = int(std::min<int64_t>(k + idx->pad, 2048));
+  if (idx->ntotal > 0 && idx->engine != B2R_ENGINE_FMA && !force_fma) {
+    const int kp_tc = idx->storage == B2R_STORE_F32 ? int(k + std::max(idx->pad, 22)) : kp;
+    use_umma = umma_supported(idx->storage, int(idx->d), kp_tc, idx->ntotal);
+    if (use_umma) kp = kp_tc;
+    else if (idx->engine == B2R_ENGINE_UMMA)
+      return fail(B2R_ERR_LIMIT, "the tcgen05 engine does not take this shape (storage %d, d %lld, k' %d)", idx->storage, (long long)idx->d, kp_tc);
+  }
   int launches = 0;
   const int ldq = idx->ld;
-  RC_TRY(idx->qf.ensure(size_t(nq) * ldq * 4));
+  RC_TRY(idx->qf.ensure(size_t(nq + 256) * ldq * 4));
   RC_TRY(idx->qh.ensure(size_t(nq + 256) * ldq * 2));
   RC_TRY(idx->qn2.ensure(size_t(nq) * 4));
   RC_TRY(idx->thr.ensure(size_t(nq) * 4));
@@ -413,12 +427,6 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   if (idx->ntotal > 0) {
     const int slot = int(idx->nrec % b2r_index::kEvPool);
     CU_TRY(cudaEventRecord(idx->ev0[slot], st));
-    bool use_umma = false;
-    if (idx->engine != B2R_ENGINE_FMA) {
-      use_umma = umma_supported(idx->storage, int(idx->d), kp, idx->ntotal);
-      if (!use_umma && idx->engine == B2R_ENGINE_UMMA)
-        return fail(B2R_ERR_LIMIT, "the tcgen05 engine does not take this shape (storage %d, d %lld, k' %d)", idx->storage, (long long)idx->d, kp);
-    }
     if (use_umma) {
       UmmaCall uc{};
       uc.X = idx->X; uc.n = idx->ntotal; uc.ld = idx->ld; uc.d = int(idx->d); uc.storage = idx->storage;
@@ -498,7 +506,20 @@ static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int
     Dd = static_cast<float*>(idx->stage_d.p);
     Id = static_cast<int64_t*>(idx->stage_i.p);
   }
-  RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st));
+  RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, false));
+  idx->last.fallback = 0;
+  if (idx->last.engine == B2R_ENGINE_UMMA && idx->storage == B2R_STORE_F32 && idx->verify) {
+    // exact mode on the tensor cores is only as good as its proof: read the counter of unproven queries and, if
+    // any, search again with the fp32 FMA engine (whose bound is ~4000x tighter).  Costs one stream sync.
+    CU_TRY(cudaMemcpyAsync(idx->host_flag, idx->stats.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    if (*idx->host_flag != 0ull) {
+      const int l0 = idx->last.launches;
+      RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, true));
+      idx->last.fallback = 1;
+      idx->last.launches += l0;
+    }
+  }
   if (!packed && !out_dev) {
     CU_TRY(cudaMemcpyAsync(D, Dd, size_t(nq) * k * 4, cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaMemcpyAsync(I, Id, size_t(nq) * k * 8, cudaMemcpyDeviceToHost, st));

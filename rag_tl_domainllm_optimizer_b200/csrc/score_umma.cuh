@@ -407,7 +407,8 @@ struct UmmaCall {
 
 inline bool umma_supported(int storage, int d, int kp, int64_t n) {
   (void)d;
-  return storage == 1 /* bf16 */ && kp <= 256 && n > 0 && n < (int64_t(1) << 31);
+  (void)storage;   // bf16 rows: kind::f16; fp32 rows: kind::tf32 (operands truncated to 10 mantissa bits)
+  return kp <= 256 && n > 0 && n < (int64_t(1) << 31);
 }
 
 inline int umma_make_map(UmmaState& S, CUtensorMap* map, bool f32, const void* base, uint64_t inner, uint64_t rows,
@@ -512,7 +513,9 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
   fp.qchunk = kUmQMax;
   fp.slot_stride = 0;
   fp.q_stride = 0;
-  fp.errfac = float((double(c.d) + 8.0) * 2.4e-7);   // (d+8) * 2^-22: fp32 accumulation inside the tensor core
+  // (d+8) * 2^-22: fp32 accumulation inside the tensor core; TF32 adds the truncation of both operands,
+  // |trunc(a) trunc(b) - ab| <= (2^-10 + 2^-10 + 2^-20) |ab|
+  fp.errfac = float((double(c.d) + 8.0) * 2.4e-7 + (f32 ? 1.96e-3 : 0.0));
 
   std::vector<CUtensorMap> tmq(nlaunch);
   std::vector<UmmaParams> pp(nlaunch);
@@ -520,7 +523,10 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
     const int q0 = l * kUmQMax;
     const int nq = std::min(kUmQMax, c.nq - q0);
     const char* qbase = f32 ? reinterpret_cast<const char*>(c.Qf) : reinterpret_cast<const char*>(c.Qh);
-    rc = umma_make_map(S, &tmq[l], f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), uint64_t(nq), uint64_t(c.ld) * esz, kUmBM, err);
+    // rows padded to whole 128-query boxes (the buffers are sized for it; rows >= nq only feed ignored outputs):
+    // boxes that stay inside the tensor avoid TMA's out-of-bounds handling on every load
+    const uint64_t nq_box = uint64_t((nq + kUmBM - 1) / kUmBM) * kUmBM;
+    rc = umma_make_map(S, &tmq[l], f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), nq_box, uint64_t(c.ld) * esz, kUmBM, err);
     if (rc) return rc;
     UmmaParams& p = pp[l];
     p = UmmaParams{};
