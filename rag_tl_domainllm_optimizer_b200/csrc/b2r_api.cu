@@ -556,7 +556,7 @@ extern "C" int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k, co
   if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int sortn = std::max(2048, host_next_pow2(int(2 * k)));
-  merge_packed_kernel<<<int(nq), 256, size_t(sortn) * 8, st>>>(packed, int(G), int(nq), int(k), sortn, metric, D, I);
+  merge_packed_kernel<<<int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st>>>(packed, int(G), int(nq), int(k), sortn, metric, D, I);
   CU_TRY(cudaGetLastError());
   return B2R_OK;
 }

@@ -43,12 +43,55 @@ struct FinalizeParams {
   unsigned long long* stats;  // [0] unverified queries, [1] candidates seen
 };
 
+// Block-wide radix select: returns the `keep`-th largest of the n distinct keys in s[0..n) (n >= keep >= 1).
+// 8 passes over 8-bit digits from the top; O(n) work instead of a full sort.  hist_s: 256 ints, sel_s: 2 ints.
+__device__ __forceinline__ uint64_t block_radix_kth(const uint64_t* s, int n, int keep, int* hist_s, int* sel_s) {
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
+  uint64_t prefix = 0ull;
+  int need = keep;
+  for (int shift = 56; shift >= 0; shift -= 8) {
+    for (int i = tid; i < 256; i += nt) hist_s[i] = 0;
+    __syncthreads();
+    const uint64_t himask = shift == 56 ? 0ull : (~0ull << (shift + 8));
+    for (int i = tid; i < n; i += nt) {
+      const uint64_t key = s[i];
+      if ((key & himask) == prefix) atomicAdd(&hist_s[int(key >> shift) & 255], 1);
+    }
+    __syncthreads();
+    if (tid < 32) {   // lane l owns digits 255-8l .. 248-8l; find the digit where the count from the top reaches `need`
+      int c[8], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { c[j] = hist_s[255 - 8 * lane - j]; sum += c[j]; }
+      int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(kFull, incl, o);
+        if (lane >= o) incl += v;
+      }
+      int above = incl - sum;   // keys with a larger digit than any of this lane's
+      if (above < need && incl >= need) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (above < need && above + c[j] >= need) { sel_s[0] = 255 - 8 * lane - j; sel_s[1] = need - above; above = need; }
+          else above += c[j];
+        }
+      }
+    }
+    __syncthreads();
+    prefix |= uint64_t(sel_s[0]) << shift;
+    need = sel_s[1];
+    __syncthreads();
+  }
+  return prefix;
+}
+
 // Gathers the keys of `nslots` lists (list s holds cnt_of(s) keys key_of(s, i)), drops zero keys and keys whose
 // score half is below thr_hi, and leaves the best `keep` in s[0..keep) sorted descending (s has sortn entries,
 // sortn >= keep + blockDim).  Returns min(#kept keys, keep).  Block-collective; off_s is [kFinMaxSlots + 1] ints.
 template <typename CntF, typename KeyF>
 __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int nslots, CntF cnt_of, KeyF key_of,
-                                           uint32_t thr_hi, int* off_s, int* fill_s, unsigned long long* seen) {
+                                           uint32_t thr_hi, int* off_s, int* fill_s, unsigned long long* seen,
+                                           uint64_t* tmp /* [next_pow2(keep)] */) {
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
   for (int sl = tid; sl < nslots; sl += nt) off_s[sl + 1] = cnt_of(sl);
   if (tid == 0) { off_s[0] = 0; *fill_s = 0; }
@@ -97,12 +140,36 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
     }
     fill += __syncthreads_count(pass);
   }
+  if (seen) {   // one global atomic per warp, not per thread
+    unsigned long long w = mine;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) w += __shfl_xor_sync(kFull, w, o);
+    if (lane == 0 && w) atomicAdd(seen, w);
+  }
+  if (fill > 4 * keep && fill > 256) {
+    // many more survivors than needed: pick the best `keep` with a radix select, then sort only those
+    int* hist_s = off_s;            // the prefix sums are no longer needed
+    int* sel_s = off_s + 256;
+    const uint64_t kth = block_radix_kth(s, fill, keep, hist_s, sel_s);
+    if (tid == 0) *fill_s = 0;
+    __syncthreads();
+    for (int i = tid; i < fill; i += nt) {
+      const uint64_t key = s[i];
+      if (key >= kth) {                                   // exactly `keep` keys: they are distinct
+        const int pos = atomicAdd(fill_s, 1);
+        if (pos < keep) tmp[pos] = key;
+      }
+    }
+    __syncthreads();
+    for (int i = tid; i < keep; i += nt) s[i] = tmp[i];
+    fill = keep;
+    __syncthreads();
+  }
   int nsort = 2;
   while (nsort < fill) nsort <<= 1;
   for (int i = fill + tid; i < nsort; i += nt) s[i] = 0ull;
   __syncthreads();
   block_bitonic_desc(s, nsort);
-  if (seen && mine) atomicAdd(seen, mine);
   return min(fill, keep);
 }
 
@@ -128,7 +195,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
     if (p.interleave) return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)];
     return p.cand[slot * p.slot_stride + q * p.q_stride + i];
   };
-  const int ncand = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, thrq, off_s, &fill_s, p.stats ? p.stats + 1 : nullptr);
+  const int ncand = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, thrq, off_s, &fill_s, p.stats ? p.stats + 1 : nullptr, s2);
 
   // exact re-scoring of the survivors
   const float* qrow = p.Q + int64_t(q) * p.ldq;
@@ -196,7 +263,7 @@ __global__ void __launch_bounds__(256) merge_packed_kernel(const uint64_t* __res
   const int q = blockIdx.x;
   auto cnt_of = [&](int) -> int { return k; };
   auto key_of = [&](int g, int i) -> uint64_t { return packed[(int64_t(g) * nq + q) * k + i]; };
-  const int got = gather_topk(s, sortn, k, G, cnt_of, key_of, 0u, off_s, &fill_s, nullptr);
+  const int got = gather_topk(s, sortn, k, G, cnt_of, key_of, 0u, off_s, &fill_s, nullptr, s + sortn);
   for (int j = threadIdx.x; j < k; j += blockDim.x) {
     const bool have = j < got;
     uint64_t key = have ? s[j] : 0ull;

@@ -443,7 +443,7 @@ __global__ void __launch_bounds__(kFinThreads) seed_select_kernel(FinalizeParams
   auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
   auto cnt_of = [&](int slot) -> int { return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per))); };
   auto key_of = [&](int slot, int i) -> uint64_t { return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)]; };
-  const int got = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, 0u, off_s, &fill_s, nullptr);
+  const int got = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, 0u, off_s, &fill_s, nullptr, s + p.sortn);
   if (threadIdx.x == 0 && got == p.kp) atomicMax(thr_g + q, uint32_t(s[p.kp - 1] >> 32));
 }
 
@@ -549,11 +549,11 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
     sp.kp = c.kp;
     sp.sortn = 8192;
     if (!S.attr_set[4]) {
-      cudaError_t ea = cudaFuncSetAttribute(seed_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8);
+      cudaError_t ea = cudaFuncSetAttribute(seed_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (8192 + 512) * 8);
       if (ea != cudaSuccess) { err = std::string("seed_select attribute failed: ") + cudaGetErrorString(ea); return -2; }
       S.attr_set[4] = true;
     }
-    seed_select_kernel<<<c.nq, kFinThreads, size_t(sp.sortn) * 8, st>>>(sp, c.thr);
+    seed_select_kernel<<<c.nq, kFinThreads, size_t(sp.sortn + 512) * 8, st>>>(sp, c.thr);   // + tmp[next_pow2(kp) <= 256]
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("seed_select launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
