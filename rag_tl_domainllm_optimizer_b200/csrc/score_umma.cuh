@@ -55,6 +55,7 @@ struct UmmaParams {
   int mt_stride;      // m-tiles per CTA slot in the scratch layout (>= mtiles)
   int num_k;          // K steps per tile
   int kp, cap, kmax;
+  int bmax;           // seed bisection stops once K' <= count <= bmax (bmax <= cap - 32)
   const float* norm2; // L2 metric: |x|^2 per stored row
   uint32_t* thr_g;    // [call nq] ordered-float thresholds shared by all CTAs (0 = none yet)
   uint64_t* cand;     // [grid][mtiles][cap][128]
@@ -63,6 +64,7 @@ struct UmmaParams {
   int slot_base;      // first scratch slot of this launch (seed launch: 0, main launch: #seed CTAs)
   int bisect_first;   // seed launch: find the first tile's threshold by bisection over TMEM
   float* dbg;         // optional [nq][n] dense scores (probe only)
+  int dbg_flags;      // probe only: 1 = load the query tile once per CTA, 2 = skip the MMAs, 4 = skip the filter
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -128,6 +130,13 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&u)[32]) {
       : "memory");
 }
 
+// one fp32 column of this thread's TMEM lane (warp-collective, uniform column)
+__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
+  uint32_t v;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\ntcgen05.wait::ld.sync.aligned;" : "=r"(v) : "r"(taddr) : "memory");
+  return v;
+}
+
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (tcgen05 "smem descriptor"):
 //   bits [0,14) start address >> 4, [16,30) leading byte offset >> 4 (unused for swizzled K-major: 1),
 //   [32,46) stride byte offset >> 4 (8 rows x 128 B = 1024 B), [46,48) version = 1, [61,64) layout 2 = 128B swizzle.
@@ -181,9 +190,16 @@ __device__ __forceinline__ void compact_lanes(uint64_t* buf, uint32_t& cnt, floa
 // ---------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------
-template <bool kTf32, bool kL2>
+template <bool kTf32, bool kL2, bool kPair>
 __global__ void __launch_bounds__(kUmThreads, 1)
 score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, const UmmaParams p) {
+  // kPair: two query tiles (m, m+1) share every corpus stage — stage = A(m) 16K | A(m+1) 16K | B 32K, 3 stages —
+  // which cuts the L2->SM operand traffic per MMA by a third (the limiter at large batches); the two TMEM
+  // accumulators then belong to the two tiles of the pair.  !kPair: stage = A 16K | B 32K, 4 stages, and the two
+  // accumulators double-buffer consecutive tiles (the HBM-bound, single-tile case).
+  constexpr int kStages = kPair ? 3 : 4;
+  constexpr int kStageStride = kPair ? (2 * kUmABytes + kUmBBytes) : kUmStageBytes;
+  constexpr int kBOff = kPair ? 2 * kUmABytes : kUmABytes;
   extern __shared__ unsigned char smem_dyn[];
   // 1024-byte alignment for the 128B-swizzled stages
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
@@ -194,13 +210,13 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kUmStages);
-  const uint32_t tfull0 = smem_u32(bars + 2 * kUmStages), tempty0 = smem_u32(bars + 2 * kUmStages + 2);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
+  const uint32_t tfull0 = smem_u32(bars + 2 * kStages), tempty0 = smem_u32(bars + 2 * kStages + 2);
   const uint32_t stage0 = smem_u32(smem);
 
   for (int i = threadIdx.x; i < kUmQMax; i += blockDim.x) { thr_s[i] = -INFINITY; cnt_s[i] = 0u; }
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < kUmStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_q)) : "memory");
@@ -215,24 +231,35 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // contiguous range of corpus tiles for this CTA
-  const int64_t t0 = p.ntiles * blockIdx.x / gridDim.x, t1 = p.ntiles * (blockIdx.x + 1) / gridDim.x;
+  // work items = (corpus tile t, query-tile group mg), t-major; a CTA owns a contiguous range of items, so its
+  // corpus rows are contiguous and the re-reads of a tile by the following query tiles hit L2
+  const int mstep = kPair ? 2 : 1;
+  const int mitems = (p.mtiles + mstep - 1) / mstep;
+  const int64_t nitems = p.ntiles * mitems;
+  const int64_t i0 = nitems * blockIdx.x / gridDim.x, i1 = nitems * (blockIdx.x + 1) / gridDim.x;
   const int kelems = kTf32 ? 32 : 64;   // elements of K per stage
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
-      for (int64_t t = t0; t < t1; ++t) {
+      for (int64_t item = i0; item < i1; ++item) {
+        const int64_t t = item / mitems;
+        const int m = int(item - t * mitems) * mstep;
         const int row = int(p.row0 + t * kUmBN);
-        for (int m = 0; m < p.mtiles; ++m) {
+        {
+          const bool two = kPair && (m + 1 < p.mtiles);
           for (int k = 0; k < p.num_k; ++k) {
             mbar_wait(empty0 + 8 * stage, phase ^ 1);
-            const uint32_t sa = stage0 + stage * kUmStageBytes;
-            mbar_expect_tx(full0 + 8 * stage, kUmStageBytes);
-            tma_load_2d(sa, &tmap_q, full0 + 8 * stage, k * kelems, m * kUmBM);
-            tma_load_2d(sa + kUmABytes, &tmap_x, full0 + 8 * stage, k * kelems, row);
-            if (++stage == kUmStages) { stage = 0; phase ^= 1; }
+            const uint32_t sa = stage0 + stage * kStageStride;
+            const bool skip_a = (p.dbg_flags & 1) && (item > i0 || k >= kStages);
+            mbar_expect_tx(full0 + 8 * stage, kUmBBytes + (skip_a ? 0 : kUmABytes + (two ? kUmABytes : 0)));
+            if (!skip_a) {
+              tma_load_2d(sa, &tmap_q, full0 + 8 * stage, k * kelems, m * kUmBM);
+              if (two) tma_load_2d(sa + kUmABytes, &tmap_q, full0 + 8 * stage, k * kelems, (m + 1) * kUmBM);
+            }
+            tma_load_2d(sa + kBOff, &tmap_x, full0 + 8 * stage, k * kelems, row);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
       }
@@ -240,28 +267,44 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
-    for (int64_t t = t0; t < t1; ++t) {
-      for (int m = 0; m < p.mtiles; ++m) {
-        mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * kUmBN;
+    for (int64_t item = i0; item < i1; ++item) {
+      {
+        const int m = int(item % mitems) * mstep;
+        const bool two = kPair && (m + 1 < p.mtiles);
+        // accumulator / phase of tile m, and of tile m+1 when it shares the stages
+        const uint32_t a0 = acc, ph0 = acc_phase;
+        acc ^= 1; if (acc == 0) acc_phase ^= 1;
+        const uint32_t a1 = acc, ph1 = acc_phase;
+        if (two) { acc ^= 1; if (acc == 0) acc_phase ^= 1; }
         for (int k = 0; k < p.num_k; ++k) {
           mbar_wait(full0 + 8 * stage, phase);
+          if (k == 0) mbar_wait(tempty0 + 8 * a0, ph0 ^ 1);
           tc_fence_after();
-          if (elect_one()) {
-            const uint32_t sa = stage0 + stage * kUmStageBytes;
-            const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + kUmABytes);
+          const uint32_t sa = stage0 + stage * kStageStride;
+          const uint64_t db = make_smem_desc(sa + kBOff);
+          const bool leader = elect_one();
+          if (leader) {
+            const uint64_t da = make_smem_desc(sa);
 #pragma unroll
             for (int j = 0; j < 4; ++j)   // 4 x 32 bytes of K inside the 128-byte swizzle atom
-              tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
-            tc_commit(empty0 + 8 * stage);                       // frees the smem stage when the MMAs retire
-            if (k == p.num_k - 1) tc_commit(tfull0 + 8 * acc);   // accumulator complete
+              if (!(p.dbg_flags & 2) || (k == 0 && j == 0))
+              tc_mma<kTf32>(tmem_base + a0 * kUmBN, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
+            if (k == p.num_k - 1) tc_commit(tfull0 + 8 * a0);   // accumulator of tile m complete
           }
+          if (two) {
+            if (k == 0) { mbar_wait(tempty0 + 8 * a1, ph1 ^ 1); tc_fence_after(); }
+            if (leader) {
+              const uint64_t da = make_smem_desc(sa + kUmABytes);
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                tc_mma<kTf32>(tmem_base + a1 * kUmBN, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
+              if (k == p.num_k - 1) tc_commit(tfull0 + 8 * a1);
+            }
+          }
+          if (leader) tc_commit(empty0 + 8 * stage);             // frees the smem stage when the MMAs retire
           __syncwarp();
-          if (++stage == kUmStages) { stage = 0; phase ^= 1; }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
       }
     }
   } else {
@@ -270,35 +313,42 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int tq = quarter * 32 + lane;           // query within the tile == TMEM lane
     const int et = (warp - 2) * 32 + lane;        // 0..127 among epilogue threads
     uint32_t acc = 0, acc_phase = 0;
-    for (int64_t t = t0; t < t1; ++t) {
+    int64_t t_prev = -1;
+    for (int64_t item = i0; item < i1; ++item) {
+      const int64_t t = item / mitems;
+      const int m_first = int(item - t * mitems) * mstep;
+      const int m_last = min(p.mtiles, m_first + mstep);
+      const bool first_visit = (item - i0) < mitems;   // first time this CTA sees these query tiles
       const int64_t row = p.row0 + t * kUmBN;
       const int ncols = int(p.n - row < kUmBN ? p.n - row : kUmBN);
-      if (kL2) {
+      if (kL2 && t != t_prev) {
+        t_prev = t;
         asm volatile("bar.sync 1, 128;" ::: "memory");          // everyone done with the previous tile's norms
         for (int c = et; c < kUmBN; c += 128) hn_s[c] = c < ncols ? 0.5f * p.norm2[row + c] : 0.f;
         asm volatile("bar.sync 1, 128;" ::: "memory");
       }
-      for (int m = 0; m < p.mtiles; ++m) {
+      for (int m = m_first; m < m_last; ++m) {
         const int qi = m * kUmBM + tq;
         const bool valid_q = qi < p.nq;
         const bool warp_has_q = (m * kUmBM + quarter * 32) < p.nq;
         float thr = -INFINITY;
         uint32_t cnt = 0;
         uint32_t* thr_g_q = p.thr_g + p.q0 + (valid_q ? qi : 0);
+        uint32_t g = 0u;
         if (valid_q) {
           thr = thr_s[qi];
           cnt = cnt_s[qi];
-          uint32_t g = *reinterpret_cast<volatile uint32_t*>(thr_g_q);
-          if (g) thr = fmaxf(thr, ordered_to_f32(g));
+          g = *reinterpret_cast<volatile uint32_t*>(thr_g_q);   // issued now, consumed after the wait below
         }
         uint64_t* buf = p.cand + ((size_t(p.slot_base + blockIdx.x) * p.mt_stride + m) * p.cap) * 128 + tq;
         mbar_wait(tfull0 + 8 * acc, acc_phase);
         tc_fence_after();
+        if (g) thr = fmaxf(thr, ordered_to_f32(g));
         const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * kUmBN;
-        if (warp_has_q) {
+        if (warp_has_q && !(p.dbg_flags & 4)) {
           uint32_t u[32];
           // ---- first tile of this query in this CTA: threshold by bisection over TMEM ----
-          if (p.bisect_first && t == t0 && ncols >= p.kp) {
+          if (p.bisect_first && first_visit && ncols >= p.kp) {
             float lo = INFINITY, hi = -INFINITY;
             for (int c = 0; c < kUmBN / 32; ++c) {
               tmem_ld32(taddr + c * 32, u);
@@ -311,7 +361,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             }
             uint32_t clo = uint32_t(ncols);
             for (int it = 0; it < 24; ++it) {
-              if (!__any_sync(kFull, clo > uint32_t(p.kmax) && hi > lo)) break;
+              if (!__any_sync(kFull, clo > uint32_t(p.bmax) && hi > lo)) break;
               const float mid = 0.5f * lo + 0.5f * hi;
               uint32_t cge = 0;
               for (int c = 0; c < kUmBN / 32; ++c) {
@@ -323,7 +373,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                   cge += (c * 32 + i < ncols && s >= mid) ? 1u : 0u;
                 }
               }
-              if (clo > uint32_t(p.kmax) && hi > lo) {
+              if (clo > uint32_t(p.bmax) && hi > lo) {
                 if (!(mid > lo && mid < hi)) hi = lo;                       // cannot split further (ties / rounding)
                 else if (cge >= uint32_t(p.kp)) { lo = mid; clo = cge; }    // invariant: count(s >= lo) == clo >= kp
                 else hi = mid;
@@ -335,21 +385,55 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             }
           }
           // ---- filter + append ----
+          // Branch-free pass mask per lane (one compare per score), then a warp-uniform walk over the union of
+          // the set bits: the passing column is re-read from TMEM with a single-column load (registers cannot be
+          // indexed dynamically) and appended by the lanes whose mask has the bit.  >99% of chunks have no bit set.
           for (int c = 0; c < kUmBN / 32; ++c) {
             if (c * 32 >= ncols) break;
             const bool need = valid_q && cnt > uint32_t(p.cap - 32);
             if (__any_sync(kFull, need)) compact_lanes(buf, cnt, thr, p.kp, p.kmax, thr_g_q, need);
             tmem_ld32(taddr + c * 32, u);
-            if (valid_q) {
+            uint32_t mask = 0u;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              float s = __uint_as_float(u[i]);
+              if (kL2) s -= hn_s[c * 32 + i];
+              mask |= (s >= thr) ? (1u << i) : 0u;
+            }
+            const int left = ncols - c * 32;
+            if (left < 32) mask &= (1u << left) - 1u;
+            if (!valid_q) mask = 0u;
+            if (p.dbg && valid_q) {   // probe only: dense scores
 #pragma unroll
               for (int i = 0; i < 32; ++i) {
                 float s = __uint_as_float(u[i]);
                 if (kL2) s -= hn_s[c * 32 + i];
-                if (p.dbg && c * 32 + i < ncols) p.dbg[size_t(qi) * p.n + row + c * 32 + i] = s;
-                if (c * 32 + i < ncols && s >= thr) {
+                if (i < left) p.dbg[size_t(qi) * p.n + row + c * 32 + i] = s;
+              }
+            }
+            uint32_t any = __reduce_or_sync(kFull, mask);
+            if (__popc(any) > 6) {
+              // dense chunk (seed tile): walk the statically indexed registers instead of re-reading TMEM
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                if ((mask >> i) & 1u) {
+                  float s = __uint_as_float(u[i]);
+                  if (kL2) s -= hn_s[c * 32 + i];
                   buf[size_t(cnt) * 128] = make_key_max(s, uint32_t(row + c * 32 + i));
                   ++cnt;
                 }
+              }
+              any = 0u;
+            }
+            while (any) {
+              const int i = __ffs(any) - 1;
+              any &= any - 1u;
+              const uint32_t v = tmem_ld1(taddr + c * 32 + i);
+              if ((mask >> i) & 1u) {
+                float s = __uint_as_float(v);
+                if (kL2) s -= hn_s[c * 32 + i];
+                buf[size_t(cnt) * 128] = make_key_max(s, uint32_t(row + c * 32 + i));
+                ++cnt;
               }
             }
           }
@@ -388,7 +472,7 @@ struct UmmaState {
   PFN_encodeTiled encode = nullptr;
   void* cand = nullptr; size_t cand_bytes = 0;
   void* cnt = nullptr; size_t cnt_bytes = 0;
-  bool attr_set[5] = {false, false, false, false, false};
+  bool attr_set[9] = {false, false, false, false, false, false, false, false, false};
   void release() {
     if (cand) cudaFree(cand);
     if (cnt) cudaFree(cnt);
@@ -403,6 +487,8 @@ struct UmmaCall {
   const void* Qh; const float* Qf; int nq; int kp;
   const float* norm2; uint32_t* thr; int sm_count;
   float* dbg = nullptr;
+  int dbg_flags = 0;
+  int force_pair = -1;   // probe only: -1 auto, 0 never, 1 always
 };
 
 inline bool umma_supported(int storage, int d, int kp, int64_t n) {
@@ -455,9 +541,12 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
   // seed launch: one tile per CTA over the first rows; main launch: everything after them
   // (seed size: enough rows for a sharp threshold, few enough CTAs for a cheap selection)
   const int64_t seed_want = std::max<int64_t>(32, std::min<int64_t>(c.sm_count, ntiles / 64));
-  const int grid_seed = int(std::min<int64_t>(ntiles, seed_want));
-  const int64_t tiles_main = ntiles - grid_seed;
-  const int grid_main = int(tiles_main < c.sm_count ? tiles_main : c.sm_count);
+  const int tiles_seed = int(std::min<int64_t>(ntiles, seed_want));
+  const int64_t tiles_main = ntiles - tiles_seed;
+  const int mt_all = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
+  // CTAs: the (tile, query tile) items of a launch are spread over up to one CTA per SM
+  const int grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(tiles_seed) * mt_all));
+  const int grid_main = int(std::min<int64_t>(c.sm_count, tiles_main * mt_all));
   const int slots = grid_seed + grid_main;
   int cap = 128;
   while (cap < 4 * c.kp) cap <<= 1;
@@ -487,16 +576,23 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
   const int variant = (f32 ? 2 : 0) + (c.norm2 ? 1 : 0);
   auto launch = [&](int grid, const CUtensorMap& tmq, const UmmaParams& p) -> cudaError_t {
     cudaError_t e = cudaSuccess;
-#define B2R_UM_LAUNCH(TF, L2)                                                                                      \
+#define B2R_UM_LAUNCH(TF, L2, PR)                                                                                  \
   do {                                                                                                             \
-    if (!S.attr_set[variant]) {                                                                                    \
-      e = cudaFuncSetAttribute(score_umma_kernel<TF, L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes); \
-      if (e == cudaSuccess) S.attr_set[variant] = true;                                                            \
+    const int vi = variant * 2 + (PR ? 1 : 0);                                                                     \
+    if (!S.attr_set[vi]) {                                                                                         \
+      e = cudaFuncSetAttribute(score_umma_kernel<TF, L2, PR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes); \
+      if (e == cudaSuccess) S.attr_set[vi] = true;                                                                 \
     }                                                                                                              \
-    if (e == cudaSuccess) score_umma_kernel<TF, L2><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p);          \
+    if (e == cudaSuccess) score_umma_kernel<TF, L2, PR><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p);      \
   } while (0)
-    if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true); else B2R_UM_LAUNCH(true, false); }
-    else     { if (c.norm2) B2R_UM_LAUNCH(false, true); else B2R_UM_LAUNCH(false, false); }
+    const bool pair = c.force_pair > 0;   // pairs lose the accumulator double-buffering: kept for experiments only
+    if (pair) {
+      if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true, true); else B2R_UM_LAUNCH(true, false, true); }
+      else     { if (c.norm2) B2R_UM_LAUNCH(false, true, true); else B2R_UM_LAUNCH(false, false, true); }
+    } else {
+      if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true, false); else B2R_UM_LAUNCH(true, false, false); }
+      else     { if (c.norm2) B2R_UM_LAUNCH(false, true, false); else B2R_UM_LAUNCH(false, false, false); }
+    }
 #undef B2R_UM_LAUNCH
     if (e == cudaSuccess) e = cudaGetLastError();
     return e;
@@ -525,19 +621,19 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
     const char* qbase = f32 ? reinterpret_cast<const char*>(c.Qf) : reinterpret_cast<const char*>(c.Qh);
     // rows padded to whole 128-query boxes (the buffers are sized for it; rows >= nq only feed ignored outputs):
     // boxes that stay inside the tensor avoid TMA's out-of-bounds handling on every load
-    const uint64_t nq_box = uint64_t((nq + kUmBM - 1) / kUmBM) * kUmBM;
+    const uint64_t nq_box = uint64_t((nq + 2 * kUmBM - 1) / (2 * kUmBM)) * (2 * kUmBM);
     rc = umma_make_map(S, &tmq[l], f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), nq_box, uint64_t(c.ld) * esz, kUmBM, err);
     if (rc) return rc;
     UmmaParams& p = pp[l];
     p = UmmaParams{};
     p.n = c.n; p.nq = nq; p.q0 = q0; p.mtiles = (nq + kUmBM - 1) / kUmBM; p.mt_stride = mt_max; p.num_k = num_k;
-    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.norm2 = c.norm2; p.thr_g = c.thr;
+    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.bmax = cap - 40; p.norm2 = c.norm2; p.thr_g = c.thr;
     p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * slots * mt_max * cap * 128;
     p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * slots * mt_max * 128;
     p.idesc = (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
-    p.dbg = c.dbg;
+    p.dbg = c.dbg; p.dbg_flags = c.dbg_flags;
     // seed launch
-    p.row0 = 0; p.ntiles = grid_seed; p.slot_base = 0; p.bisect_first = 1;
+    p.row0 = 0; p.ntiles = tiles_seed; p.slot_base = 0; p.bisect_first = 1;
     cudaError_t e = launch(grid_seed, tmq[l], p);
     if (e != cudaSuccess) { err = std::string("tcgen05 seed launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
@@ -548,10 +644,10 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
     sp.nslots = grid_seed;
     sp.kp = c.kp;
     sp.sortn = 8192;
-    if (!S.attr_set[4]) {
+    if (!S.attr_set[8]) {
       cudaError_t ea = cudaFuncSetAttribute(seed_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (8192 + 512) * 8);
       if (ea != cudaSuccess) { err = std::string("seed_select attribute failed: ") + cudaGetErrorString(ea); return -2; }
-      S.attr_set[4] = true;
+      S.attr_set[8] = true;
     }
     seed_select_kernel<<<c.nq, kFinThreads, size_t(sp.sortn + 512) * 8, st>>>(sp, c.thr);   // + tmp[next_pow2(kp) <= 256]
     cudaError_t e = cudaGetLastError();
@@ -559,7 +655,7 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
     ++*launches;
     for (int l = 0; l < nlaunch; ++l) {
       UmmaParams& p = pp[l];
-      p.row0 = int64_t(grid_seed) * kUmBN; p.ntiles = tiles_main; p.slot_base = grid_seed; p.bisect_first = 0;
+      p.row0 = int64_t(tiles_seed) * kUmBN; p.ntiles = tiles_main; p.slot_base = grid_seed; p.bisect_first = 0;
       e = launch(grid_main, tmq[l], p);
       if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
       ++*launches;

@@ -167,12 +167,61 @@ static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_
   return (bad || unwritten || missing) ? 3 : 0;
 }
 
+__global__ void fill_kernel(uint32_t* p, size_t n, uint32_t seed, int f32) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    uint32_t h = uint32_t(i) * 2654435761u + seed; h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+    float v = (float(h & 0xffff) / 65536.f - 0.5f) * 0.1f;
+    if (f32) p[i] = __float_as_uint(v);
+    else { __nv_bfloat162 b = __floats2bfloat162_rn(v, -v); p[i] = *reinterpret_cast<uint32_t*>(&b); }
+  }
+}
+
+// perf mode: no verification, device-generated data, timing of the launch set under diagnostic flags
+static int run_perf(int64_t n, int nq, int d, bool f32, int flags, int pairmode, int sm_count) {
+  const int ld = (d + 63) / 64 * 64;
+  const size_t esz = f32 ? 4 : 2;
+  void *dX, *dQ; uint32_t* dthr;
+  CK(cudaMalloc(&dX, size_t(n) * ld * esz));
+  CK(cudaMalloc(&dQ, size_t(nq + 256) * ld * esz));
+  CK(cudaMalloc(&dthr, nq * 4));
+  fill_kernel<<<1024, 256>>>(reinterpret_cast<uint32_t*>(dX), size_t(n) * ld * esz / 4, 1u, f32);
+  fill_kernel<<<64, 256>>>(reinterpret_cast<uint32_t*>(dQ), size_t(nq + 256) * ld * esz / 4, 7u, f32);
+  UmmaState S;
+  UmmaCall c{};
+  c.X = dX; c.n = n; c.ld = ld; c.d = d; c.storage = f32 ? 0 : 1;
+  c.Qh = dQ; c.Qf = reinterpret_cast<const float*>(dQ); c.nq = nq; c.kp = 16;
+  c.norm2 = nullptr; c.thr = dthr; c.sm_count = sm_count; c.dbg_flags = flags; c.force_pair = pairmode;
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  float best = 1e9f;
+  for (int it = 0; it < 5; ++it) {
+    CK(cudaMemset(dthr, 0, nq * 4));
+    FinalizeParams fp{}; int launches = 0; std::string err;
+    cudaEventRecord(e0);
+    int rc = umma_launch(S, c, nullptr, fp, &launches, err);
+    cudaEventRecord(e1);
+    if (rc) { printf("launch failed: %s\n", err.c_str()); return 1; }
+    cudaError_t se = cudaDeviceSynchronize();
+    if (se != cudaSuccess) { printf("KERNEL FAULT: %s\n", cudaGetErrorString(se)); return 2; }
+    float ms; cudaEventElapsedTime(&ms, e0, e1);
+    best = std::min(best, ms);
+  }
+  const double bytes = double(n) * ld * esz, flops = 2.0 * nq * double(n) * d;
+  printf("perf n=%lld nq=%d d=%d %s flags=%d pair=%d: %.3f ms  corpus %.2f TB/s  %.0f TFLOP/s\n", (long long)n, nq, d,
+         f32 ? "tf32" : "bf16", flags, pairmode, best, bytes / best / 1e9, flops / best / 1e9);
+  S.release(); cudaFree(dX); cudaFree(dQ); cudaFree(dthr);
+  return 0;
+}
+
 int main(int argc, char** argv) {
   int dev = 0, sm = 148;
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) { printf("no CUDA device\n"); return 1; }
   sm = prop.multiProcessorCount;
   printf("device: %s, %d SMs\n", prop.name, sm);
+  if (argc > 1 && !strcmp(argv[1], "perf")) {
+    // perf <n> <nq> <d> <f32> <flags> <pair>
+    return run_perf(atoll(argv[2]), atoi(argv[3]), atoi(argv[4]), atoi(argv[5]) != 0, atoi(argv[6]), atoi(argv[7]), sm);
+  }
   int fails = 0;
   struct C { int64_t n; int nq, d, kp; bool f32, l2; };
   const C cases[] = {
