@@ -231,19 +231,21 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // work items = (corpus tile t, query-tile group mg), t-major; a CTA owns a contiguous range of items, so its
-  // corpus rows are contiguous and the re-reads of a tile by the following query tiles hit L2
+  // work items = (corpus tile t, query-tile group mg), t-major, dealt round-robin to the CTAs: at any moment the
+  // grid works on ~gridDim/mitems neighbouring corpus tiles, so a tile is fetched from HBM once and its re-reads
+  // by the other query tiles hit L2 whatever the tile size (a contiguous split would keep gridDim different
+  // tiles live at once: 116 MB for fp32 rows of 768, more than L2 holds)
   const int mstep = kPair ? 2 : 1;
   const int mitems = (p.mtiles + mstep - 1) / mstep;
   const int64_t nitems = p.ntiles * mitems;
-  const int64_t i0 = nitems * blockIdx.x / gridDim.x, i1 = nitems * (blockIdx.x + 1) / gridDim.x;
+  const int64_t i0 = blockIdx.x, i1 = nitems, istep = gridDim.x;
   const int kelems = kTf32 ? 32 : 64;   // elements of K per stage
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
-      for (int64_t item = i0; item < i1; ++item) {
+      for (int64_t item = i0; item < i1; item += istep) {
         const int64_t t = item / mitems;
         const int m = int(item - t * mitems) * mstep;
         const int row = int(p.row0 + t * kUmBN);
@@ -267,7 +269,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
-    for (int64_t item = i0; item < i1; ++item) {
+    for (int64_t item = i0; item < i1; item += istep) {
       {
         const int m = int(item % mitems) * mstep;
         const bool two = kPair && (m + 1 < p.mtiles);
@@ -314,11 +316,14 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int et = (warp - 2) * 32 + lane;        // 0..127 among epilogue threads
     uint32_t acc = 0, acc_phase = 0;
     int64_t t_prev = -1;
-    for (int64_t item = i0; item < i1; ++item) {
+    uint32_t seen_m = 0u;   // query-tile groups this CTA has already visited (mitems <= 16)
+    for (int64_t item = i0; item < i1; item += istep) {
       const int64_t t = item / mitems;
-      const int m_first = int(item - t * mitems) * mstep;
+      const int mg = int(item - t * mitems);
+      const int m_first = mg * mstep;
       const int m_last = min(p.mtiles, m_first + mstep);
-      const bool first_visit = (item - i0) < mitems;   // first time this CTA sees these query tiles
+      const bool first_visit = !((seen_m >> mg) & 1u);   // first time this CTA sees these query tiles
+      seen_m |= 1u << mg;
       const int64_t row = p.row0 + t * kUmBN;
       const int ncols = int(p.n - row < kUmBN ? p.n - row : kUmBN);
       if (kL2 && t != t_prev) {
