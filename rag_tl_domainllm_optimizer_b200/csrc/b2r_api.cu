@@ -394,11 +394,12 @@ static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, Final
 static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t k, int normalize_queries,
                          int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st, bool force_fma) {
   // engine and K': the TF32 tensor-core pass truncates both operands to 10 mantissa bits, so it keeps a wider
-  // candidate list (pad >= 22) for the completeness proof to go through; FMA and bf16 (exact products) keep pad.
+  // candidate list (K' >= 2k, at least k + 22) for the completeness proof to go through; FMA and bf16 (exact products) keep pad.
   bool use_umma = false;
-  int kp = int(std::min<int64_t>(k + idx->pad, 2048));
+  // the candidate pad grows with k: the gaps between neighbouring scores shrink like 1/rank
+  int kp = int(std::min<int64_t>(k + std::max<int64_t>(idx->pad, k / 8), 2048));
   if (idx->ntotal > 0 && idx->engine != B2R_ENGINE_FMA && !force_fma) {
-    const int kp_tc = idx->storage == B2R_STORE_F32 ? int(k + std::max(idx->pad, 22)) : kp;
+    const int kp_tc = idx->storage == B2R_STORE_F32 ? int(k + std::max<int64_t>(std::max(idx->pad, 22), k)) : kp;
     use_umma = umma_supported(idx->storage, int(idx->d), kp_tc, idx->ntotal);
     if (use_umma) kp = kp_tc;
     else if (idx->engine == B2R_ENGINE_UMMA)

@@ -614,9 +614,12 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
   fp.qchunk = kUmQMax;
   fp.slot_stride = 0;
   fp.q_stride = 0;
-  // (d+8) * 2^-22: fp32 accumulation inside the tensor core; TF32 adds the truncation of both operands,
-  // |trunc(a) trunc(b) - ab| <= (2^-10 + 2^-10 + 2^-20) |ab|
-  fp.errfac = float((double(c.d) + 8.0) * 2.4e-7 + (f32 ? 1.96e-3 : 0.0));
+  // Error model of the tensor-core pass, relative to |q||x|: products of bf16 (or truncated-TF32) operands are
+  // exact; every tcgen05.mma folds its K-slice (16 bf16 / 8 tf32 products) into the fp32 accumulator, charged
+  // here with 2 ulp (2^-23) of the running magnitude per instruction: (d/8 + 8) * 2^-23 for bf16,
+  // (d/4 + 8) * 2^-23 for tf32 (measured: 2.8e-7 at d=768, tools/umma_probe, 40x below this).  TF32 adds the
+  // truncation of both operands: |trunc(a) trunc(b) - ab| <= (2^-10 + 2^-10 + 2^-20) |ab|.
+  fp.errfac = float(f32 ? (double(c.d) / 4 + 8.0) * 1.1921e-7 + 1.96e-3 : (double(c.d) / 8 + 8.0) * 1.1921e-7);
 
   std::vector<CUtensorMap> tmq(nlaunch);
   std::vector<UmmaParams> pp(nlaunch);

@@ -1,0 +1,121 @@
+"""GPU parity at the shapes of BASELINE.json's other configs (reduced row counts so the oracle finishes in
+seconds), the multi-launch path (more than 2048 queries), the proof/fallback path, and size-independent
+properties at the full 1M x 768 size of configs[1]."""
+import numpy as np
+import pytest
+
+import rag_tl_domainllm_optimizer_b200 as b2r
+
+pytestmark = pytest.mark.gpu
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def _check(D, I, D0, I0):
+    assert np.array_equal(np.asarray(I), I0)
+    assert np.array_equal(_bits(D), _bits(D0))
+
+
+def _data(oracle, n, d, nq, seed0):
+    x = oracle.normalize(oracle.synth_rows(seed0, 0, n, d))
+    q = oracle.normalize(oracle.synth_rows(seed0 + 1, 0, nq, d))
+    return x, q
+
+
+@pytest.mark.parametrize("storage", ["f32", "bf16"])
+def test_config3_shape_bge_large_k100(oracle, storage):
+    """configs[2] shape: d=1024, batch 256, k=100 (one shard's worth of rows, reduced)."""
+    x, q = _data(oracle, 60_000, 1024, 256, 30)
+    idx = b2r.IndexFlatIP(1024, storage=storage)
+    idx.add(x)
+    D, I = idx.search(q, 100)
+    if storage == "bf16":
+        x, q = oracle.round_bf16(x), oracle.round_bf16(q)
+    _check(D, I, *oracle.search_ref(x, q, 100, 0, extra=100))
+    st = idx.last_stats()
+    assert st["engine"] == b2r.ENGINE_UMMA and st["unverified"] == 0
+
+
+@pytest.mark.parametrize("storage", ["f32", "bf16"])
+def test_config4_shape_llama_hidden_k4(oracle, storage):
+    """configs[3] shape: d=4096 (LLaMA-2-7B hidden size), 256 queries per step, k=4 gold+distractor docs."""
+    x, q = _data(oracle, 20_000, 4096, 256, 40)
+    idx = b2r.IndexFlatIP(4096, storage=storage)
+    idx.add(x)
+    D, I = idx.search(q, 4)
+    if storage == "bf16":
+        x, q = oracle.round_bf16(x), oracle.round_bf16(q)
+    _check(D, I, *oracle.search_ref(x, q, 4, 0))
+    assert idx.last_stats()["unverified"] == 0
+
+
+def test_config5_shape_batch4096_bf16(oracle):
+    """configs[4] shape: d=768 bf16, batch 4096 (two query chunks of 2048 per scoring launch set), k=10."""
+    x, q = _data(oracle, 100_000, 768, 4096, 50)
+    idx = b2r.IndexFlatIP(768, storage="bf16")
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    _check(D, I, *oracle.search_ref(oracle.round_bf16(x), oracle.round_bf16(q), 10, 0))
+    st = idx.last_stats()
+    assert st["unverified"] == 0 and st["nq"] == 4096
+
+
+def test_unproven_search_falls_back_and_stays_exact(oracle):
+    """60 exact copies of one row: the gap between the k-th and the K'-th candidate is zero, so the tensor-core
+    pass cannot prove completeness; the call must repeat on the FMA engine and still return the lowest ids."""
+    x, q = _data(oracle, 30_000, 256, 4, 60)
+    x[1000:1060] = x[7]
+    q[0] = x[7]
+    idx = b2r.IndexFlatIP(256)
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    _check(D, I, *oracle.search_ref(x, q, 10, 0, extra=128))
+    assert I[0, 0] == 7 and list(I[0, 1:]) == list(range(1000, 1009))
+    st = idx.last_stats()
+    assert st["fallback"] == 1 and st["engine"] == b2r.ENGINE_FMA
+
+
+def test_full_size_properties_1m_768(oracle):
+    """configs[1] at full size (1M x 768): properties that need no full oracle run."""
+    import torch
+    n, d, k = 1_000_000, 768, 10
+    g = torch.Generator(device="cuda")
+    g.manual_seed(123)
+    x = torch.randn((n, d), generator=g, device="cuda")
+    b2r.normalize_L2(x)
+    sel = torch.arange(0, n, n // 96, device="cuda")[:96]
+    q = x[sel].contiguous()
+    exact = b2r.IndexFlatIP(d)
+    exact.add(x)
+    D, I = exact.search(q, k)
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    assert np.array_equal(I[:, 0], sel.cpu().numpy())                    # a stored row retrieves itself first
+    assert np.all(np.abs(D[:, 0] - 1.0) < 1e-6)
+    assert np.all(D[:, :-1] >= D[:, 1:])                                 # best first
+    assert all(len(set(r)) == k for r in I)                             # no id twice
+    assert exact.last_stats()["unverified"] == 0
+    # a slice of the batch against the defined oracle on the same rows (32 queries x 1M rows, fp64 BLAS + DOT64)
+    xh = x.cpu().numpy()
+    D0, I0 = oracle.search_ref(xh, q[:32].cpu().numpy(), k, 0)
+    _check(D[:32], I[:32], D0, I0)
+    # idempotence: same call, same bits
+    D2, I2 = exact.search(q, k)
+    assert np.array_equal(I2.cpu().numpy(), I) and np.array_equal(_bits(D2.cpu().numpy()), _bits(D))
+    # row-sharded (G=4) == unsharded, through the packed merge
+    packs = []
+    for r in range(4):
+        lo, hi = b2r.shard_bounds(n, 4, r)
+        sh = b2r.IndexFlatIP(d)
+        sh.add(x[lo:hi])
+        packs.append(sh.search_packed(q, k, lo))
+        del sh
+    Dm, Im = b2r.merge_packed(torch.stack(packs), 0)
+    assert np.array_equal(Im.cpu().numpy(), I) and np.array_equal(_bits(Dm.cpu().numpy()), _bits(D))
+    # fast mode: recall against exact mode
+    fast = b2r.IndexFlatIP(d, storage="bf16")
+    fast.add(x)
+    _, If = fast.search(q, k)
+    rec = np.mean([len(set(a) & set(b)) / k for a, b in zip(If.cpu().numpy(), I)])
+    assert rec >= 0.9
