@@ -452,7 +452,9 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   }
   fp.thr = static_cast<const uint32_t*>(idx->thr.p);
   fp.nq = int(nq); fp.kp = kp; fp.k = int(k);
-  fp.sortn = std::max(4096, host_next_pow2(kp + kFinThreads));
+  // few queries: one big CTA per query (latency); many queries: small CTAs, several per SM (throughput)
+  const int fin_threads = nq >= 256 ? 256 : kFinThreads;
+  fp.sortn = std::max(4096, host_next_pow2(kp + fin_threads));
   fp.X = idx->X; fp.ld = idx->ld; fp.d = int(idx->d); fp.storage = idx->storage;
   fp.Q = static_cast<const float*>(idx->qf.p); fp.ldq = ldq; fp.qn2 = static_cast<const float*>(idx->qn2.p);
   fp.metric = idx->metric; fp.n = idx->ntotal; fp.row_offset = row_offset;
@@ -462,10 +464,10 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   const size_t smem = size_t(fp.sortn + host_next_pow2(kp)) * 8;
   if (idx->storage == B2R_STORE_BF16) {
     CU_TRY(cudaFuncSetAttribute(finalize_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    finalize_kernel<__nv_bfloat16><<<int(nq), kFinThreads, smem, st>>>(fp);
+    finalize_kernel<__nv_bfloat16><<<int(nq), fin_threads, smem, st>>>(fp);
   } else {
     CU_TRY(cudaFuncSetAttribute(finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    finalize_kernel<float><<<int(nq), kFinThreads, smem, st>>>(fp);
+    finalize_kernel<float><<<int(nq), fin_threads, smem, st>>>(fp);
   }
   CU_TRY(cudaGetLastError());
   ++launches;

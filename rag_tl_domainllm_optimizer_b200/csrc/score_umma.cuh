@@ -536,6 +536,13 @@ __global__ void __launch_bounds__(kFinThreads) seed_select_kernel(FinalizeParams
   auto key_of = [&](int slot, int i) -> uint64_t { return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)]; };
   const int got = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, 0u, off_s, &fill_s, nullptr, s + p.sortn);
   if (threadIdx.x == 0 && got == p.kp) atomicMax(thr_g + q, uint32_t(s[p.kp - 1] >> 32));
+  // Leave only the survivors behind: the best K' of the seed rows go to seed slot 0, the other seed slots of
+  // this query are emptied, so the final merge gathers K' seed entries instead of every seed CTA's list.
+  uint64_t* cand_w = const_cast<uint64_t*>(p.cand);
+  uint32_t* cnt_w = const_cast<uint32_t*>(p.cnt);
+  __syncthreads();
+  for (int i = threadIdx.x; i < got; i += blockDim.x) cand_w[(blk_of(0) * p.per + i) * 128 + (ql & 127)] = s[i];
+  for (int sl = threadIdx.x; sl < p.nslots; sl += blockDim.x) cnt_w[blk_of(sl) * 128 + (ql & 127)] = sl == 0 ? uint32_t(got) : 0u;
 }
 
 inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
@@ -546,11 +553,16 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
   // seed launch: one tile per CTA over the first rows; main launch: everything after them
   // (seed size: enough rows for a sharp threshold, few enough CTAs for a cheap selection)
   const int64_t seed_want = std::max<int64_t>(32, std::min<int64_t>(c.sm_count, ntiles / 64));
-  const int tiles_seed = int(std::min<int64_t>(ntiles, seed_want));
-  const int64_t tiles_main = ntiles - tiles_seed;
   const int mt_all = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
+  const int seed_cap = mt_all > 1 ? c.sm_count - (c.sm_count - 1) % mt_all : c.sm_count;   // see grid_seed below
+  const int tiles_seed = int(std::min<int64_t>(std::min<int64_t>(ntiles, seed_want), seed_cap));
+  const int64_t tiles_main = ntiles - tiles_seed;
   // CTAs: the (tile, query tile) items of a launch are spread over up to one CTA per SM
-  const int grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(tiles_seed) * mt_all));
+  // seed grid: with round-robin items CTA b visits query tile (b + j*grid) % mt on its j-th item; a grid size that
+  // is 1 modulo mt makes consecutive visits hit different query tiles, so every (CTA, query) gets exactly one seed
+  // tile and its threshold comes from the in-TMEM bisection (a second visit would flood the buffer)
+  int grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(tiles_seed) * mt_all));
+  if (mt_all > 1 && int64_t(tiles_seed) * mt_all > grid_seed) grid_seed -= (grid_seed - 1) % mt_all;
   const int grid_main = int(std::min<int64_t>(c.sm_count, tiles_main * mt_all));
   const int slots = grid_seed + grid_main;
   int cap = 128;
@@ -657,7 +669,7 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
       if (ea != cudaSuccess) { err = std::string("seed_select attribute failed: ") + cudaGetErrorString(ea); return -2; }
       S.attr_set[8] = true;
     }
-    seed_select_kernel<<<c.nq, kFinThreads, size_t(sp.sortn + 512) * 8, st>>>(sp, c.thr);   // + tmp[next_pow2(kp) <= 256]
+    seed_select_kernel<<<c.nq, c.nq >= 256 ? 256 : kFinThreads, size_t(sp.sortn + 512) * 8, st>>>(sp, c.thr);   // + tmp[next_pow2(kp) <= 256]
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("seed_select launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
