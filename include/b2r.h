@@ -77,6 +77,9 @@ typedef struct b2r_search_stats {
   int32_t fallback;       /* 1 if an exact-mode tensor-core search could not be proven  */
                           /* and the call was repeated on the fp32 FMA engine           */
   int32_t reserved;
+  int64_t main_rows;      /* rows covered by the launch(es) that b2r_index_score_time times: */
+                          /* the main tcgen05 launch (all rows but the seed rows), or all    */
+                          /* rows for the FMA engine                                         */
 } b2r_search_stats;
 
 /* Library / device ------------------------------------------------------------------ */
@@ -170,7 +173,8 @@ int b2r_index_last_stats(b2r_index* idx, b2r_search_stats* out);
  * roofline figure. */
 int b2r_index_last_score_ms(b2r_index* idx, float* ms);
 
-/* Sum of the scoring-kernel times (ms, CUDA events on the search's stream) of the searches
+/* Sum of the dominant scoring launches' times (main tcgen05 launch, or all FMA passes; ms,
+ * CUDA events on the search's stream; rows covered: b2r_search_stats.main_rows) of the searches
  * made since the last reset (at most the 256 most recent), and how many they were;
  * reset != 0 clears the record afterwards.  Synchronises.  No faiss counterpart: it exists so
  * that bench.py can report the dominant kernel's duration over its own timed region. */

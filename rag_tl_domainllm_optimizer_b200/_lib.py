@@ -34,7 +34,8 @@ EXPORTS = [
 class SearchStats(ctypes.Structure):
     _fields_ = [("nq", ctypes.c_int64), ("k", ctypes.c_int64), ("kprime", ctypes.c_int64),
                 ("unverified", ctypes.c_int64), ("candidates", ctypes.c_int64), ("engine", ctypes.c_int32),
-                ("launches", ctypes.c_int32), ("fallback", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+                ("launches", ctypes.c_int32), ("fallback", ctypes.c_int32), ("reserved", ctypes.c_int32),
+                ("main_rows", ctypes.c_int64)]
 
 
 class B2RError(RuntimeError):

@@ -425,9 +425,10 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   }
   FinalizeParams fp{};
   int engine_used = B2R_ENGINE_FMA;
+  int64_t main_rows = idx->ntotal;
   if (idx->ntotal > 0) {
     const int slot = int(idx->nrec % b2r_index::kEvPool);
-    CU_TRY(cudaEventRecord(idx->ev0[slot], st));
+    if (!use_umma) CU_TRY(cudaEventRecord(idx->ev0[slot], st));
     if (use_umma) {
       UmmaCall uc{};
       uc.X = idx->X; uc.n = idx->ntotal; uc.ld = idx->ld; uc.d = int(idx->d); uc.storage = idx->storage;
@@ -435,14 +436,20 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
       uc.norm2 = idx->metric == B2R_METRIC_L2 ? idx->norm2 : nullptr;
       uc.thr = static_cast<uint32_t*>(idx->thr.p);
       uc.sm_count = idx->sm_count;
+      uc.ev_main0 = idx->ev0[slot]; uc.ev_main1 = idx->ev1[slot];   // the timers bracket the main launch
       std::string err;
       int rc = umma_launch(idx->umma, uc, st, fp, &launches, err);
       if (rc != B2R_OK) return fail(rc, "%s", err.c_str());
       engine_used = B2R_ENGINE_UMMA;
+      main_rows = uc.main_rows;
+      if (main_rows == 0) {   // tiny index: everything ran in the seed launch; nothing to time separately
+        CU_TRY(cudaEventRecord(idx->ev0[slot], st));
+        CU_TRY(cudaEventRecord(idx->ev1[slot], st));
+      }
     } else {
       RC_TRY(launch_fma(idx, nq, kp, st, fp, &launches));
+      CU_TRY(cudaEventRecord(idx->ev1[slot], st));
     }
-    CU_TRY(cudaEventRecord(idx->ev1[slot], st));
     ++idx->nrec;
     idx->have_times = true;
   } else {
@@ -473,7 +480,7 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   ++launches;
   idx->last = b2r_search_stats{};
   idx->last.nq = nq; idx->last.k = k; idx->last.kprime = kp;
-  idx->last.engine = engine_used; idx->last.launches = launches;
+  idx->last.engine = engine_used; idx->last.launches = launches; idx->last.main_rows = main_rows;
   return B2R_OK;
 }
 

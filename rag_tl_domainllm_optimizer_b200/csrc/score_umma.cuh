@@ -494,6 +494,8 @@ struct UmmaCall {
   float* dbg = nullptr;
   int dbg_flags = 0;
   int force_pair = -1;   // probe only: -1 auto, 0 never, 1 always
+  cudaEvent_t ev_main0 = nullptr, ev_main1 = nullptr;   // optional: recorded around the main launch(es)
+  int64_t main_rows = 0;                                // out: rows the main launch(es) cover
 };
 
 inline bool umma_supported(int storage, int d, int kp, int64_t n) {
@@ -545,7 +547,7 @@ __global__ void __launch_bounds__(kFinThreads) seed_select_kernel(FinalizeParams
   for (int sl = threadIdx.x; sl < p.nslots; sl += blockDim.x) cnt_w[blk_of(sl) * 128 + (ql & 127)] = sl == 0 ? uint32_t(got) : 0u;
 }
 
-inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
+inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
   const bool f32 = c.storage == 0;
   const int kelems = f32 ? 32 : 64;
   const int num_k = (c.d + kelems - 1) / kelems;
@@ -673,6 +675,8 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("seed_select launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
+    if (c.ev_main0) cudaEventRecord(c.ev_main0, st);
+    c.main_rows = c.n - int64_t(tiles_seed) * kUmBN;
     for (int l = 0; l < nlaunch; ++l) {
       UmmaParams& p = pp[l];
       p.row0 = int64_t(tiles_seed) * kUmBN; p.ntiles = tiles_main; p.slot_base = grid_seed; p.bisect_first = 0;
@@ -680,6 +684,10 @@ inline int umma_launch(UmmaState& S, const UmmaCall& c, cudaStream_t st, Finaliz
       if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
       ++*launches;
     }
+    if (c.ev_main1) cudaEventRecord(c.ev_main1, st);
+  } else {
+    // the seed launch was the whole search
+    c.main_rows = 0;
   }
   return 0;
 }
