@@ -124,6 +124,16 @@ int b2r_index_ntotal(const b2r_index* idx, int64_t* out);
  * Replaces faiss `Index::reconstruct(i, out)`. */
 int b2r_index_reconstruct(b2r_index* idx, int64_t i, float* out, void* stream);
 
+/* Copy n stored rows starting at row0 out in their STORED representation: dense [n,d] float32
+ * (exact mode) or bfloat16 (fast mode), exactly the values search() scores.  `out` may be a host or
+ * a device pointer.  With b2r_index_import_rows this is the per-rank shard save/load
+ * (SURVEY.md §8 f3); the faiss counterpart is `write_index` / `read_index` on an IndexFlat. */
+int b2r_index_export_rows(b2r_index* idx, int64_t row0, int64_t n, void* out, void* stream);
+
+/* Append n rows given in the STORED representation (as b2r_index_export_rows wrote them): no
+ * normalisation, no rounding; row norms are recomputed on the device. */
+int b2r_index_import_rows(b2r_index* idx, int64_t n, const void* rows, void* stream);
+
 /* Search ---------------------------------------------------------------------------- */
 
 /* Exact top-k over all stored rows for nq queries (fp32 [nq,d]).

@@ -27,7 +27,7 @@ EXPORTS = [
     "b2r_index_reserve", "b2r_index_reset", "b2r_index_ntotal", "b2r_index_reconstruct", "b2r_index_search",
     "b2r_index_search_ex", "b2r_index_search_packed", "b2r_merge_packed", "b2r_index_set_engine",
     "b2r_index_set_pad", "b2r_index_last_stats", "b2r_index_last_score_ms", "b2r_index_score_time", "b2r_normalize_l2", "b2r_cosine_rows",
-    "b2r_cosine_rows_noalloc",
+    "b2r_cosine_rows_noalloc", "b2r_index_export_rows", "b2r_index_import_rows",
 ]
 
 
@@ -77,6 +77,8 @@ def lib() -> ctypes.CDLL:
     L.b2r_index_reset.argtypes = [vp]
     L.b2r_index_ntotal.argtypes = [vp, ctypes.POINTER(i64)]
     L.b2r_index_reconstruct.argtypes = [vp, i64, vp, vp]
+    L.b2r_index_export_rows.argtypes = [vp, i64, i64, vp, vp]
+    L.b2r_index_import_rows.argtypes = [vp, i64, vp, vp]
     L.b2r_index_search.argtypes = [vp, i64, vp, i64, vp, vp, vp]
     L.b2r_index_search_ex.argtypes = [vp, i64, vp, i64, i32, i64, vp, vp, vp]
     L.b2r_index_search_packed.argtypes = [vp, i64, vp, i64, i32, i64, vp, vp]

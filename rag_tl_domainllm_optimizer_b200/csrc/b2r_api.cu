@@ -760,3 +760,47 @@ extern "C" int b2r_cosine_rows_noalloc(int64_t n, int64_t m, int64_t d, const fl
   CU_TRY(cudaGetLastError());
   return B2R_OK;
 }
+
+// --------------------------------------------------------------------------------------
+// shard export / import (stored representation, no re-normalisation, no re-rounding)
+// --------------------------------------------------------------------------------------
+extern "C" int b2r_index_export_rows(b2r_index* idx, int64_t row0, int64_t n, void* out, void* stream) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (row0 < 0 || n < 0 || row0 + n > idx->ntotal) return fail(B2R_ERR_ARG, "rows [%lld, %lld) out of range (ntotal %lld)", (long long)row0, (long long)(row0 + n), (long long)idx->ntotal);
+  if (n == 0) return B2R_OK;
+  if (!out) return fail(B2R_ERR_ARG, "out is null");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t esz = idx->elem_bytes(), w = size_t(idx->d) * esz;
+  const char* src = static_cast<const char*>(idx->X) + size_t(row0) * idx->ld * esz;
+  CU_TRY(cudaMemcpy2DAsync(out, w, src, size_t(idx->ld) * esz, w, size_t(n), cudaMemcpyDefault, st));
+  if (!is_device_ptr(out)) CU_TRY(cudaStreamSynchronize(st));
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_import_rows(b2r_index* idx, int64_t n, const void* rows, void* stream) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (n < 0) return fail(B2R_ERR_ARG, "negative row count");
+  if (n == 0) return B2R_OK;
+  if (!rows) return fail(B2R_ERR_ARG, "rows is null");
+  if (idx->ntotal + n > 0xfffffffeLL) return fail(B2R_ERR_LIMIT, "a shard holds at most 2^32-2 rows");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RC_TRY(grow(idx, idx->ntotal + n, st));
+  const size_t esz = idx->elem_bytes(), w = size_t(idx->d) * esz, pitch = size_t(idx->ld) * esz;
+  char* dst = static_cast<char*>(idx->X) + size_t(idx->ntotal) * pitch;
+  if (pitch != w) CU_TRY(cudaMemsetAsync(dst, 0, size_t(n) * pitch, st));   // zero padding of every row
+  CU_TRY(cudaMemcpy2DAsync(dst, pitch, rows, w, w, size_t(n), cudaMemcpyDefault, st));
+  const int blocks = int(std::min<int64_t>((n + 7) / 8, int64_t(idx->sm_count) * 16));
+  float* n2 = idx->norm2 ? idx->norm2 + idx->ntotal : nullptr;
+  if (idx->storage == B2R_STORE_BF16)
+    row_norms_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dst), n, int(idx->d), idx->ld, n2, idx->maxnorm2);
+  else
+    row_norms_kernel<float><<<blocks, 256, 0, st>>>(reinterpret_cast<const float*>(dst), n, int(idx->d), idx->ld, n2, idx->maxnorm2);
+  CU_TRY(cudaGetLastError());
+  if (!is_device_ptr(rows)) CU_TRY(cudaStreamSynchronize(st));   // the caller may reuse its host buffer
+  idx->ntotal += n;
+  return B2R_OK;
+}

@@ -171,3 +171,22 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
 }
 
 }  // namespace b2r
+
+namespace b2r {
+// Squared norms of already-stored rows (shard import): norm2[r] = fp32 of DOT64(x_r, x_r); maxnorm2 raised likewise.
+template <typename T>
+__global__ void __launch_bounds__(256) row_norms_kernel(const T* __restrict__ X, int64_t n, int d, int ld,
+                                                        float* __restrict__ norm2, float* __restrict__ maxnorm2) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  float wmax = 0.f;
+  for (int64_t r = warp0; r < n; r += nwarps) {
+    const T* x = X + r * int64_t(ld);
+    const float n2 = float(warp_reduce64<Red::kDot>(x, x, d, lane));
+    if (norm2 && lane == 0) norm2[r] = n2;
+    wmax = fmaxf(wmax, n2);
+  }
+  if (maxnorm2 && lane == 0 && wmax > 0.f) atomicMax(reinterpret_cast<int*>(maxnorm2), __float_as_int(wmax));
+}
+}  // namespace b2r

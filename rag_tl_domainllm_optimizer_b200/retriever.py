@@ -36,6 +36,14 @@ class FlatRetriever:
             out.append([(self.passages[int(i)], float(s)) for s, i in zip(drow, irow) if i >= 0])
         return out
 
+    def retrieve_raft(self, query_embeddings, gold_ids, k: int, k_prime: int | None = None, p_gold: float = 1.0,
+                      seed: int = 0) -> List[List[str]]:
+        """Gold + distractor passages per query (RAFT rollout sets): search top-k', then ``raft_select``."""
+        k_prime = k_prime or 2 * k
+        _, I = self.index.search(np.ascontiguousarray(query_embeddings, dtype=np.float32), k_prime)
+        ids, _ = raft_select(np.asarray(I), gold_ids, k, p_gold, seed)
+        return [[self.passages[int(j)] for j in row if j >= 0] for row in ids]
+
     def retrieve(self, query_embeddings, k: int) -> List[List[str]]:
         """-> one ``list[str]`` of up to k passages per query, best first (the ``retrieved_docs`` contract)."""
         return [[p for p, _ in row] for row in self.search_with_scores(query_embeddings, k)]
@@ -50,3 +58,30 @@ def collate_retrieval_batch(items: Sequence[dict]) -> dict:
     """
     keys = items[0].keys() if items else []
     return {key: [it[key] for it in items] for key in keys}
+
+
+def raft_select(I, gold_ids, k: int, p_gold: float = 1.0, seed: int = 0):
+    """RAFT-style document sets from a top-k' search result (reference README.md:2, config 4).
+
+    For each query: the gold document (``gold_ids[i]``; kept with probability ``p_gold``, as RAFT trains a share
+    of samples without it) plus distractors = the best-ranked retrieved ids that are not the gold one, ``k`` ids in
+    all, then shuffled so that the gold position carries no signal.  ``I`` is the ``[n, k']`` id matrix of a search
+    with k' >= k (``-1`` = no hit).  Returns (ids [n, k] int64 with -1 padding, gold_pos [n] int64, -1 if absent).
+    Pure index bookkeeping on the search output — the search itself is the GPU path.
+    """
+    I = np.asarray(I)
+    n = I.shape[0]
+    rng = np.random.default_rng(seed)
+    out = np.full((n, k), -1, dtype=np.int64)
+    gold_pos = np.full(n, -1, dtype=np.int64)
+    for i in range(n):
+        gold = int(gold_ids[i])
+        keep_gold = gold >= 0 and rng.random() < p_gold
+        distractors = [int(j) for j in I[i] if j >= 0 and int(j) != gold]
+        docs = ([gold] if keep_gold else []) + distractors[: k - (1 if keep_gold else 0)]
+        order = rng.permutation(len(docs))
+        docs = [docs[j] for j in order]
+        out[i, : len(docs)] = docs
+        if keep_gold:
+            gold_pos[i] = docs.index(gold)
+    return out, gold_pos

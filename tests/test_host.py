@@ -48,3 +48,23 @@ def test_collate_keeps_per_sample_lists():
     batch = b2r.collate_retrieval_batch(items)
     pairs = list(zip(batch["query"], batch["retrieved_docs"]))              # the zip at reference :292
     assert pairs == [("q0", ["a", "b"]), ("q1", ["c", "d"]), ("q2", ["e", "f"])]
+
+
+def test_raft_select_gold_plus_distractors():
+    I = np.array([[5, 9, 2, 7, 1, 3], [4, 8, 6, 0, -1, -1], [1, 2, 3, 4, 5, 6]], dtype=np.int64)
+    gold = [2, 33, 6]                      # in the hits / not retrieved at all / last of the hits
+    ids, pos = b2r.raft_select(I, gold, k=4, p_gold=1.0, seed=3)
+    for row, g, p in zip(ids, gold, pos):
+        assert row[p] == g and list(row).count(g) == 1            # gold present exactly once, position reported
+    assert sorted(ids[0]) == [2, 5, 7, 9]                          # gold + the 3 best-ranked non-gold hits
+    assert sorted(ids[1]) == [4, 6, 8, 33]
+    assert sorted(ids[2]) == [1, 2, 3, 6]
+    ids0, pos0 = b2r.raft_select(I, gold, k=4, p_gold=0.0, seed=3)  # RAFT's "no gold" share: distractors only
+    assert np.all(pos0 == -1) and sorted(ids0[0]) == [5, 7, 9, 1] or sorted(ids0[0]) == [1, 5, 7, 9]
+    assert 2 not in ids0[0]
+    a, _ = b2r.raft_select(I, gold, 4, 1.0, seed=11)
+    b, _ = b2r.raft_select(I, gold, 4, 1.0, seed=11)
+    assert np.array_equal(a, b)                                    # deterministic in the seed
+    r = b2r.FlatRetriever(_FakeIndex(np.zeros((3, 6), np.float32), I), [f"p{i}" for i in range(40)])
+    docs = r.retrieve_raft(np.zeros((3, 4), np.float32), gold, k=4, k_prime=6, seed=3)
+    assert [len(d) for d in docs] == [4, 4, 4] and "p2" in docs[0] and "p33" in docs[1]
