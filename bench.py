@@ -155,7 +155,7 @@ def run_reference(args, rank, world):
 
 
 def workload_config(args, world):
-    return {"workload": f"configs[1]: {args.rows}x{DIM} corpus, query batch {args.batch}, k={args.k}, "
+    return {"workload": f"{'configs[1]: ' if (args.rows, DIM) == (N_ROWS, 768) else ''}{args.rows}x{DIM} corpus, query batch {args.batch}, k={args.k}, "
                         f"{'exact fp32' if args.mode == 'exact' else 'bf16'} inner-product flat search",
             "rows": args.rows, "dim": DIM, "batch": args.batch, "k": args.k, "mode": args.mode,
             "sharding": f"rows/{world}" if world > 1 else "none",
@@ -163,6 +163,7 @@ def workload_config(args, world):
 
 
 def main():
+    global DIM
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -171,6 +172,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--k", type=int, default=K)
     ap.add_argument("--rows", type=int, default=N_ROWS)
+    ap.add_argument("--dim", type=int, default=DIM, help="embedding dimension (other BASELINE configs)")
     ap.add_argument("--mode", default="exact", choices=["exact", "bf16"])
     ap.add_argument("--engine", type=int, default=0)
     ap.add_argument("--sweep", default="1,8,32,128,1024", help="comma list of extra batch sizes ('' = none)")
@@ -178,6 +180,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--check-queries", type=int, default=32)
     args = ap.parse_args()
+    DIM = args.dim
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
 
     rank = int(os.environ.get("RANK", "0"))

@@ -92,6 +92,7 @@ template <typename CntF, typename KeyF>
 __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int nslots, CntF cnt_of, KeyF key_of,
                                            uint32_t thr_hi, int* off_s, int* fill_s, unsigned long long* seen,
                                            uint64_t* tmp /* [next_pow2(keep)] */) {
+  __shared__ int hist_sh[258];   // radix-select histogram + its two result words
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
   for (int sl = tid; sl < nslots; sl += nt) off_s[sl + 1] = cnt_of(sl);
   if (tid == 0) { off_s[0] = 0; *fill_s = 0; }
@@ -115,11 +116,20 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
   int fill = 0;   // uniform copy of *fill_s
   unsigned long long mine = 0;
   for (int base = 0; base < total; base += nt) {
-    if (fill + nt > sortn) {   // make room: keep the best `keep` so far
-      for (int i = fill + tid; i < sortn; i += nt) s[i] = 0ull;
+    if (fill + nt > sortn) {   // make room: keep the best `keep` so far (radix select + compaction, O(fill))
+      const uint64_t kth = block_radix_kth(s, fill, keep, hist_sh, hist_sh + 256);
+      if (tid == 0) *fill_s = 0;
       __syncthreads();
-      block_bitonic_desc(s, sortn);
-      fill = min(fill, keep);
+      for (int i = tid; i < fill; i += nt) {
+        const uint64_t key = s[i];
+        if (key >= kth) {
+          const int pos = atomicAdd(fill_s, 1);
+          if (pos < keep) tmp[pos] = key;
+        }
+      }
+      __syncthreads();
+      for (int i = tid; i < keep; i += nt) s[i] = tmp[i];
+      fill = keep;
       if (tid == 0) *fill_s = fill;
       __syncthreads();
     }
@@ -148,9 +158,7 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
   }
   if (fill > 4 * keep && fill > 256) {
     // many more survivors than needed: pick the best `keep` with a radix select, then sort only those
-    int* hist_s = off_s;            // the prefix sums are no longer needed
-    int* sel_s = off_s + 256;
-    const uint64_t kth = block_radix_kth(s, fill, keep, hist_s, sel_s);
+    const uint64_t kth = block_radix_kth(s, fill, keep, hist_sh, hist_sh + 256);
     if (tid == 0) *fill_s = 0;
     __syncthreads();
     for (int i = tid; i < fill; i += nt) {

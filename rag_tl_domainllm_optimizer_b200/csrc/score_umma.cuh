@@ -649,7 +649,7 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     UmmaParams& p = pp[l];
     p = UmmaParams{};
     p.n = c.n; p.nq = nq; p.q0 = q0; p.mtiles = (nq + kUmBM - 1) / kUmBM; p.mt_stride = mt_max; p.num_k = num_k;
-    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.bmax = cap - 40; p.norm2 = c.norm2; p.thr_g = c.thr;
+    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.bmax = std::min(cap - 40, std::max(2 * c.kp, c.kp + 56)); p.norm2 = c.norm2; p.thr_g = c.thr;
     p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * slots * mt_max * cap * 128;
     p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * slots * mt_max * 128;
     p.idesc = (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
