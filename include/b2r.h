@@ -60,7 +60,10 @@ enum { B2R_STORE_F32 = 0, B2R_STORE_BF16 = 1 };
 enum {
   B2R_ENGINE_AUTO = 0,  /* tcgen05 tensor-core kernel when the shape allows, else FMA */
   B2R_ENGINE_FMA = 1,   /* CUDA-core fp32 FMA streaming kernel                        */
-  B2R_ENGINE_UMMA = 2   /* TMA + tcgen05.mma + TMEM kernel (bf16, or split-TF32)      */
+  B2R_ENGINE_UMMA = 2,  /* TMA + tcgen05.mma + TMEM kernel: kind::f16 on bf16 rows,   */
+                        /* one kind::tf32 pass on fp32 rows                           */
+  B2R_ENGINE_UMMA3 = 3  /* the same kernel with the 3xTF32 split (fp32 rows): the     */
+                        /* fallback of exact mode when the 1xTF32 proof fails         */
 };
 
 /* Counters of the most recent search on a handle (b2r_index_last_stats). */
@@ -72,10 +75,10 @@ typedef struct b2r_search_stats {
                           /* error bound of the scoring pass; 0 means  */
                           /* the returned ids are provably the exact top-k              */
   int64_t candidates;     /* candidate entries that reached the merge kernel            */
-  int32_t engine;         /* B2R_ENGINE_FMA or B2R_ENGINE_UMMA actually used            */
+  int32_t engine;         /* B2R_ENGINE_FMA / _UMMA / _UMMA3 actually used              */
   int32_t launches;       /* kernels launched by the call                               */
   int32_t fallback;       /* 1 if an exact-mode tensor-core search could not be proven  */
-                          /* and the call was repeated on the fp32 FMA engine           */
+                          /* and the call was repeated with 3xTF32 (or the FMA engine)   */
   int32_t reserved;
   int64_t main_rows;      /* rows covered by the launch(es) that b2r_index_score_time times: */
                           /* the main tcgen05 launch (all rows but the seed rows), or all    */

@@ -19,7 +19,7 @@ METRIC_INNER_PRODUCT = 0
 METRIC_L2 = 1
 STORE_F32 = 0
 STORE_BF16 = 1
-ENGINE_AUTO, ENGINE_FMA, ENGINE_UMMA = 0, 1, 2
+ENGINE_AUTO, ENGINE_FMA, ENGINE_UMMA, ENGINE_UMMA3 = 0, 1, 2, 3
 
 # every symbol include/b2r.h declares (tests check that the library exports all of them)
 EXPORTS = [

@@ -139,7 +139,7 @@ struct b2r_index {
   bool verify = true;                  // exact mode: re-run unproven tensor-core searches on the FMA engine
   unsigned long long* host_flag = nullptr;   // pinned, for that check
   // per-search workspace
-  DevBuf qf, qh, qn2, thr, cand, cnt, stats, stage_q, stage_d, stage_i, stage_x, misc;
+  DevBuf qf, qh, qlo, qn2, thr, cand, cnt, stats, stage_q, stage_d, stage_i, stage_x, misc;
   static constexpr int kEvPool = 256;           // scoring-kernel timers: one event pair per recent search
   cudaEvent_t ev0[kEvPool] = {}, ev1[kEvPool] = {};
   int64_t nrec = 0;                             // searches timed since the last timer reset
@@ -195,7 +195,7 @@ extern "C" void b2r_index_free(b2r_index* idx) {
   if (idx->norm2) cudaFree(idx->norm2);
   if (idx->maxnorm2) cudaFree(idx->maxnorm2);
   if (idx->host_flag) cudaFreeHost(idx->host_flag);
-  DevBuf* bufs[] = {&idx->qf, &idx->qh, &idx->qn2, &idx->thr, &idx->cand, &idx->cnt, &idx->stats,
+  DevBuf* bufs[] = {&idx->qf, &idx->qh, &idx->qlo, &idx->qn2, &idx->thr, &idx->cand, &idx->cnt, &idx->stats,
                     &idx->stage_q, &idx->stage_d, &idx->stage_i, &idx->stage_x, &idx->misc};
   for (DevBuf* b : bufs) b->release();
   idx->umma.release();
@@ -337,7 +337,7 @@ extern "C" int b2r_index_reconstruct(b2r_index* idx, int64_t i, float* out, void
 
 extern "C" int b2r_index_set_engine(b2r_index* idx, int engine) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
-  if (engine < B2R_ENGINE_AUTO || engine > B2R_ENGINE_UMMA) return fail(B2R_ERR_ARG, "unknown engine %d", engine);
+  if (engine < B2R_ENGINE_AUTO || engine > B2R_ENGINE_UMMA3) return fail(B2R_ERR_ARG, "unknown engine %d", engine);
   idx->engine = engine;
   return B2R_OK;
 }
@@ -392,23 +392,29 @@ static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, Final
 }
 
 static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t k, int normalize_queries,
-                         int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st, bool force_fma) {
-  // engine and K': the TF32 tensor-core pass truncates both operands to 10 mantissa bits, so it keeps a wider
-  // candidate list (K' >= 2k, at least k + 22) for the completeness proof to go through; FMA and bf16 (exact products) keep pad.
-  bool use_umma = false;
-  // the candidate pad grows with k: the gaps between neighbouring scores shrink like 1/rank
+                         int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st, int force_engine) {
+  // engine and K'.  The 1xTF32 tensor-core pass truncates both operands to 10 mantissa bits, so it keeps a wider
+  // candidate list (K' >= 2k, at least k + 22) for the completeness proof to go through; FMA, bf16 (exact
+  // products) and 3xTF32 keep k + pad.  The pad grows with k: gaps between neighbouring scores shrink like 1/rank.
+  const int engine = force_engine ? force_engine : idx->engine;
+  bool use_umma = false, split = false;
   int kp = int(std::min<int64_t>(k + std::max<int64_t>(idx->pad, k / 8), 2048));
-  if (idx->ntotal > 0 && idx->engine != B2R_ENGINE_FMA && !force_fma) {
-    const int kp_tc = idx->storage == B2R_STORE_F32 ? int(k + std::max<int64_t>(std::max(idx->pad, 22), k)) : kp;
+  if (idx->ntotal > 0 && engine != B2R_ENGINE_FMA) {
+    split = engine == B2R_ENGINE_UMMA3;
+    if (split && idx->storage != B2R_STORE_F32)
+      return fail(B2R_ERR_ARG, "the 3xTF32 engine needs fp32 rows (exact mode)");
+    const int kp_tc = (idx->storage == B2R_STORE_F32 && !split) ? int(k + std::max<int64_t>(std::max(idx->pad, 22), k)) : kp;
     use_umma = umma_supported(idx->storage, int(idx->d), kp_tc, idx->ntotal);
     if (use_umma) kp = kp_tc;
-    else if (idx->engine == B2R_ENGINE_UMMA)
+    else if (engine == B2R_ENGINE_UMMA || engine == B2R_ENGINE_UMMA3)
       return fail(B2R_ERR_LIMIT, "the tcgen05 engine does not take this shape (storage %d, d %lld, k' %d)", idx->storage, (long long)idx->d, kp_tc);
+    if (!use_umma) split = false;
   }
   int launches = 0;
   const int ldq = idx->ld;
   RC_TRY(idx->qf.ensure(size_t(nq + 256) * ldq * 4));
   RC_TRY(idx->qh.ensure(size_t(nq + 256) * ldq * 2));
+  if (split) RC_TRY(idx->qlo.ensure(size_t(nq + 256) * ldq * 4));
   RC_TRY(idx->qn2.ensure(size_t(nq) * 4));
   RC_TRY(idx->thr.ensure(size_t(nq) * 4));
   RC_TRY(idx->stats.ensure(2 * sizeof(unsigned long long)));
@@ -419,7 +425,7 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
     prep_queries_kernel<<<blocks, 256, 0, st>>>(q_dev, nq, int(idx->d), ldq, normalize_queries,
                                                 idx->storage == B2R_STORE_BF16, static_cast<float*>(idx->qf.p),
                                                 idx->storage == B2R_STORE_BF16 ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
-                                                static_cast<float*>(idx->qn2.p));
+                                                static_cast<float*>(idx->qn2.p), split ? static_cast<float*>(idx->qlo.p) : nullptr);
     CU_TRY(cudaGetLastError());
     ++launches;
   }
@@ -436,11 +442,12 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
       uc.norm2 = idx->metric == B2R_METRIC_L2 ? idx->norm2 : nullptr;
       uc.thr = static_cast<uint32_t*>(idx->thr.p);
       uc.sm_count = idx->sm_count;
+      uc.split = split; uc.Qlo = split ? static_cast<const float*>(idx->qlo.p) : nullptr;
       uc.ev_main0 = idx->ev0[slot]; uc.ev_main1 = idx->ev1[slot];   // the timers bracket the main launch
       std::string err;
       int rc = umma_launch(idx->umma, uc, st, fp, &launches, err);
       if (rc != B2R_OK) return fail(rc, "%s", err.c_str());
-      engine_used = B2R_ENGINE_UMMA;
+      engine_used = split ? B2R_ENGINE_UMMA3 : B2R_ENGINE_UMMA;
       main_rows = uc.main_rows;
       if (main_rows == 0) {   // tiny index: everything ran in the seed launch; nothing to time separately
         CU_TRY(cudaEventRecord(idx->ev0[slot], st));
@@ -516,16 +523,19 @@ static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int
     Dd = static_cast<float*>(idx->stage_d.p);
     Id = static_cast<int64_t*>(idx->stage_i.p);
   }
-  RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, false));
+  RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, 0));
   idx->last.fallback = 0;
   if (idx->last.engine == B2R_ENGINE_UMMA && idx->storage == B2R_STORE_F32 && idx->verify) {
     // exact mode on the tensor cores is only as good as its proof: read the counter of unproven queries and, if
-    // any, search again with the fp32 FMA engine (whose bound is ~4000x tighter).  Costs one stream sync.
+    // any, search again with the 3xTF32 split (error bound ~30x tighter; FMA engine where tcgen05 cannot take the
+    // shape).  Costs one stream sync per search.
     CU_TRY(cudaMemcpyAsync(idx->host_flag, idx->stats.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
     if (*idx->host_flag != 0ull) {
       const int l0 = idx->last.launches;
-      RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, true));
+      const int kp3 = int(k + std::max<int64_t>(idx->pad, k / 8));
+      const int fb = umma_supported(idx->storage, int(idx->d), kp3, idx->ntotal) ? B2R_ENGINE_UMMA3 : B2R_ENGINE_FMA;
+      RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, fb));
       idx->last.fallback = 1;
       idx->last.launches += l0;
     }

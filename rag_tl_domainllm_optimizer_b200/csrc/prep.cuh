@@ -139,7 +139,8 @@ __global__ void finish_maxcos_kernel(const uint32_t* __restrict__ maxord, int64_
 // of the prepared query (fp32 of DOT64).  One warp per query.
 __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, int64_t nq, int d, int ldq,
                                                            int normalize, int round_bf16, float* __restrict__ qf,
-                                                           __nv_bfloat16* __restrict__ qh, float* __restrict__ qn2) {
+                                                           __nv_bfloat16* __restrict__ qh, float* __restrict__ qn2,
+                                                           float* __restrict__ qlo /* optional: q - trunc_tf32(q) */) {
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
@@ -164,6 +165,12 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
       }
       st4(qf + r * int64_t(ldq) + c, make_float4(v[0], v[1], v[2], v[3]));
       if (qh) st4(qh + r * int64_t(ldq) + c, make_float4(v[0], v[1], v[2], v[3]));
+      if (qlo) {
+        float l[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) l[t] = v[t] - __uint_as_float(__float_as_uint(v[t]) & 0xffffe000u);
+        st4(qlo + r * int64_t(ldq) + c, make_float4(l[0], l[1], l[2], l[3]));
+      }
     }
     acc = butterfly64(acc);
     if (lane == 0) qn2[r] = float(acc);

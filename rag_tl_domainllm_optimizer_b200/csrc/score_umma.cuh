@@ -41,7 +41,8 @@ constexpr int kUmABytes = kUmBM * kUmRowBytes;        // 16 KB
 constexpr int kUmBBytes = kUmBN * kUmRowBytes;        // 32 KB
 constexpr int kUmStageBytes = kUmABytes + kUmBBytes;  // 48 KB
 constexpr int kUmQMax = 2048;       // queries per launch (thresholds / counters live in shared memory)
-constexpr int kUmThreads = 192;
+constexpr int kUmThreads = 192;        // TMA warp, MMA warp, 4 epilogue warps
+constexpr int kUmThreadsSplit = 320;   // + 4 splitter warps (3xTF32 variant)
 constexpr int kUmSmemState = kUmStages * kUmStageBytes;                 // thr_s follows the stages
 constexpr int kUmSmemBytes = kUmSmemState + kUmQMax * 8 + kUmBN * 4 + 256 + 1024;  // + alignment slack
 
@@ -190,16 +191,21 @@ __device__ __forceinline__ void compact_lanes(uint64_t* buf, uint32_t& cnt, floa
 // ---------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------
-template <bool kTf32, bool kL2, bool kPair>
-__global__ void __launch_bounds__(kUmThreads, 1)
-score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, const UmmaParams p) {
-  // kPair: two query tiles (m, m+1) share every corpus stage — stage = A(m) 16K | A(m+1) 16K | B 32K, 3 stages —
-  // which cuts the L2->SM operand traffic per MMA by a third (the limiter at large batches); the two TMEM
-  // accumulators then belong to the two tiles of the pair.  !kPair: stage = A 16K | B 32K, 4 stages, and the two
-  // accumulators double-buffer consecutive tiles (the HBM-bound, single-tile case).
-  constexpr int kStages = kPair ? 3 : 4;
-  constexpr int kStageStride = kPair ? (2 * kUmABytes + kUmBBytes) : kUmStageBytes;
-  constexpr int kBOff = kPair ? 2 * kUmABytes : kUmABytes;
+template <bool kTf32, bool kL2, bool kSplit>
+__global__ void __launch_bounds__(kUmThreadsSplit, 1)
+score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_qlo,
+                  const __grid_constant__ CUtensorMap tmap_x, const UmmaParams p) {
+  // !kSplit: stage = A 16K | B 32K, 4 stages.
+  // kSplit (3xTF32, fp32 rows only): stage = A 16K | A_lo 16K | B 32K | B_lo 32K, 2 stages.  The tensor core
+  // truncates fp32 operands to TF32, so A and B as loaded ARE the high parts; A_lo = q - trunc(q) is prepared on
+  // the host side of the launch, B_lo = x - trunc(x) is computed from the landed tile by 4 splitter warps
+  // (element-wise, so the swizzled layout needs no decoding).  Each K-step then issues q_hi.x_hi + q_lo.x_hi +
+  // q_hi.x_lo into the same accumulator: fp32-grade scores (dropped term <= 2^-20) at 3x the MMA work.
+  constexpr int kStages = kSplit ? 2 : 4;
+  constexpr int kStageStride = kSplit ? 2 * (kUmABytes + kUmBBytes) : kUmStageBytes;
+  constexpr int kAloOff = kUmABytes;
+  constexpr int kBOff = kSplit ? 2 * kUmABytes : kUmABytes;
+  constexpr int kBloOff = kBOff + kUmBBytes;
   extern __shared__ unsigned char smem_dyn[];
   // 1024-byte alignment for the 128B-swizzled stages
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
@@ -212,11 +218,16 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
   const uint32_t tfull0 = smem_u32(bars + 2 * kStages), tempty0 = smem_u32(bars + 2 * kStages + 2);
+  const uint32_t split0 = smem_u32(bars + 2 * kStages + 4);   // kSplit: "B_lo written" per stage
   const uint32_t stage0 = smem_u32(smem);
 
   for (int i = threadIdx.x; i < kUmQMax; i += blockDim.x) { thr_s[i] = -INFINITY; cnt_s[i] = 0u; }
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+      if (kSplit) mbar_init(split0 + 8 * s, 4);
+    }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_q)) : "memory");
@@ -231,12 +242,11 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // work items = (corpus tile t, query-tile group mg), t-major, dealt round-robin to the CTAs: at any moment the
-  // grid works on ~gridDim/mitems neighbouring corpus tiles, so a tile is fetched from HBM once and its re-reads
-  // by the other query tiles hit L2 whatever the tile size (a contiguous split would keep gridDim different
-  // tiles live at once: 116 MB for fp32 rows of 768, more than L2 holds)
-  const int mstep = kPair ? 2 : 1;
-  const int mitems = (p.mtiles + mstep - 1) / mstep;
+  // work items = (corpus tile t, query tile m), t-major, dealt round-robin to the CTAs: at any moment the grid
+  // works on ~gridDim/mtiles neighbouring corpus tiles, so a tile is fetched from HBM once and its re-reads by the
+  // other query tiles hit L2 whatever the tile size (a contiguous split would keep gridDim different tiles live
+  // at once: 116 MB for fp32 rows of 768, more than L2 holds)
+  const int mitems = p.mtiles;
   const int64_t nitems = p.ntiles * mitems;
   const int64_t i0 = blockIdx.x, i1 = nitems, istep = gridDim.x;
   const int kelems = kTf32 ? 32 : 64;   // elements of K per stage
@@ -247,22 +257,19 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       uint32_t stage = 0, phase = 0;
       for (int64_t item = i0; item < i1; item += istep) {
         const int64_t t = item / mitems;
-        const int m = int(item - t * mitems) * mstep;
+        const int m = int(item - t * mitems);
         const int row = int(p.row0 + t * kUmBN);
-        {
-          const bool two = kPair && (m + 1 < p.mtiles);
-          for (int k = 0; k < p.num_k; ++k) {
-            mbar_wait(empty0 + 8 * stage, phase ^ 1);
-            const uint32_t sa = stage0 + stage * kStageStride;
-            const bool skip_a = (p.dbg_flags & 1) && (item > i0 || k >= kStages);
-            mbar_expect_tx(full0 + 8 * stage, kUmBBytes + (skip_a ? 0 : kUmABytes + (two ? kUmABytes : 0)));
-            if (!skip_a) {
-              tma_load_2d(sa, &tmap_q, full0 + 8 * stage, k * kelems, m * kUmBM);
-              if (two) tma_load_2d(sa + kUmABytes, &tmap_q, full0 + 8 * stage, k * kelems, (m + 1) * kUmBM);
-            }
-            tma_load_2d(sa + kBOff, &tmap_x, full0 + 8 * stage, k * kelems, row);
-            if (++stage == kStages) { stage = 0; phase ^= 1; }
+        for (int k = 0; k < p.num_k; ++k) {
+          mbar_wait(empty0 + 8 * stage, phase ^ 1);
+          const uint32_t sa = stage0 + stage * kStageStride;
+          const bool skip_a = (p.dbg_flags & 1) && (item > i0 || k >= kStages);
+          mbar_expect_tx(full0 + 8 * stage, kUmBBytes + (skip_a ? 0 : (kSplit ? 2 : 1) * kUmABytes));
+          if (!skip_a) {
+            tma_load_2d(sa, &tmap_q, full0 + 8 * stage, k * kelems, m * kUmBM);
+            if (kSplit) tma_load_2d(sa + kAloOff, &tmap_qlo, full0 + 8 * stage, k * kelems, m * kUmBM);
           }
+          tma_load_2d(sa + kBOff, &tmap_x, full0 + 8 * stage, k * kelems, row);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -270,46 +277,62 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // ===================== MMA issuer =====================
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
     for (int64_t item = i0; item < i1; item += istep) {
-      {
-        const int m = int(item % mitems) * mstep;
-        const bool two = kPair && (m + 1 < p.mtiles);
-        // accumulator / phase of tile m, and of tile m+1 when it shares the stages
-        const uint32_t a0 = acc, ph0 = acc_phase;
-        acc ^= 1; if (acc == 0) acc_phase ^= 1;
-        const uint32_t a1 = acc, ph1 = acc_phase;
-        if (two) { acc ^= 1; if (acc == 0) acc_phase ^= 1; }
-        for (int k = 0; k < p.num_k; ++k) {
-          mbar_wait(full0 + 8 * stage, phase);
-          if (k == 0) mbar_wait(tempty0 + 8 * a0, ph0 ^ 1);
-          tc_fence_after();
+      mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * kUmBN;
+      for (int k = 0; k < p.num_k; ++k) {
+        mbar_wait((kSplit ? split0 : full0) + 8 * stage, phase);   // split done implies the TMA data landed
+        tc_fence_after();
+        if (elect_one()) {
           const uint32_t sa = stage0 + stage * kStageStride;
-          const uint64_t db = make_smem_desc(sa + kBOff);
-          const bool leader = elect_one();
-          if (leader) {
-            const uint64_t da = make_smem_desc(sa);
+          const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + kBOff);
 #pragma unroll
-            for (int j = 0; j < 4; ++j)   // 4 x 32 bytes of K inside the 128-byte swizzle atom
-              if (!(p.dbg_flags & 2) || (k == 0 && j == 0))
-              tc_mma<kTf32>(tmem_base + a0 * kUmBN, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
-            if (k == p.num_k - 1) tc_commit(tfull0 + 8 * a0);   // accumulator of tile m complete
-          }
-          if (two) {
-            if (k == 0) { mbar_wait(tempty0 + 8 * a1, ph1 ^ 1); tc_fence_after(); }
-            if (leader) {
-              const uint64_t da = make_smem_desc(sa + kUmABytes);
+          for (int j = 0; j < 4; ++j)   // 4 x 32 bytes of K inside the 128-byte swizzle atom
+            if (!(p.dbg_flags & 2) || (k == 0 && j == 0))
+              tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
+          if (kSplit) {
+            const uint64_t dalo = make_smem_desc(sa + kAloOff), dblo = make_smem_desc(sa + kBloOff);
 #pragma unroll
-              for (int j = 0; j < 4; ++j)
-                tc_mma<kTf32>(tmem_base + a1 * kUmBN, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
-              if (k == p.num_k - 1) tc_commit(tfull0 + 8 * a1);
+            for (int j = 0; j < 4; ++j) {
+              tc_mma<kTf32>(tmem_d, dalo + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, 1u);   // q_lo . x_hi
+              tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), dblo + uint64_t(2 * j), p.idesc, 1u);   // q_hi . x_lo
             }
           }
-          if (leader) tc_commit(empty0 + 8 * stage);             // frees the smem stage when the MMAs retire
-          __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          tc_commit(empty0 + 8 * stage);                       // frees the smem stage when the MMAs retire
+          if (k == p.num_k - 1) tc_commit(tfull0 + 8 * acc);   // accumulator complete
         }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  } else if (kSplit && warp >= 6) {
+    // ===================== splitter: B_lo = x - trunc_tf32(x), element-wise on the landed tile =====================
+    const int st_tid = (warp - 6) * 32 + lane;   // 0..127
+    uint32_t stage = 0, phase = 0;
+    for (int64_t item = i0; item < i1; item += istep) {
+      for (int k = 0; k < p.num_k; ++k) {
+        mbar_wait(full0 + 8 * stage, phase);
+        const uint4* src = reinterpret_cast<const uint4*>(smem + stage * kStageStride + kBOff);
+        uint4* dst = reinterpret_cast<uint4*>(smem + stage * kStageStride + kBloOff);
+#pragma unroll 4
+        for (int i = st_tid; i < kUmBBytes / 16; i += 128) {
+          const uint4 v = src[i];
+          uint4 o;
+          o.x = __float_as_uint(__uint_as_float(v.x) - __uint_as_float(v.x & 0xffffe000u));
+          o.y = __float_as_uint(__uint_as_float(v.y) - __uint_as_float(v.y & 0xffffe000u));
+          o.z = __float_as_uint(__uint_as_float(v.z) - __uint_as_float(v.z & 0xffffe000u));
+          o.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(v.w & 0xffffe000u));
+          dst[i] = o;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+        __syncwarp();
+        if (lane == 0) mbar_arrive(split0 + 8 * stage);
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
-  } else {
+  } else if (warp < 6) {
     // ===================== epilogue: thread = query =====================
     const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
     const int tq = quarter * 32 + lane;           // query within the tile == TMEM lane
@@ -320,8 +343,8 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     for (int64_t item = i0; item < i1; item += istep) {
       const int64_t t = item / mitems;
       const int mg = int(item - t * mitems);
-      const int m_first = mg * mstep;
-      const int m_last = min(p.mtiles, m_first + mstep);
+      const int m_first = mg;
+      const int m_last = mg + 1;
       const bool first_visit = !((seen_m >> mg) & 1u);   // first time this CTA sees these query tiles
       seen_m |= 1u << mg;
       const int64_t row = p.row0 + t * kUmBN;
@@ -493,7 +516,8 @@ struct UmmaCall {
   const float* norm2; uint32_t* thr; int sm_count;
   float* dbg = nullptr;
   int dbg_flags = 0;
-  int force_pair = -1;   // probe only: -1 auto, 0 never, 1 always
+  bool split = false;            // 3xTF32 (fp32 rows): needs Qlo
+  const float* Qlo = nullptr;    // q - trunc_tf32(q), same layout as Qf
   cudaEvent_t ev_main0 = nullptr, ev_main1 = nullptr;   // optional: recorded around the main launch(es)
   int64_t main_rows = 0;                                // out: rows the main launch(es) cover
 };
@@ -593,21 +617,20 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   int rc = umma_make_map(S, &tmx, f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * esz, kUmBN, err);
   if (rc) return rc;
   const int variant = (f32 ? 2 : 0) + (c.norm2 ? 1 : 0);
-  auto launch = [&](int grid, const CUtensorMap& tmq, const UmmaParams& p) -> cudaError_t {
+  auto launch = [&](int grid, const CUtensorMap& tmq, const CUtensorMap& tmqlo, const UmmaParams& p) -> cudaError_t {
     cudaError_t e = cudaSuccess;
-#define B2R_UM_LAUNCH(TF, L2, PR)                                                                                  \
+#define B2R_UM_LAUNCH(TF, L2, SP)                                                                                  \
   do {                                                                                                             \
-    const int vi = variant * 2 + (PR ? 1 : 0);                                                                     \
+    const int vi = variant * 2 + (SP ? 1 : 0);                                                                     \
     if (!S.attr_set[vi]) {                                                                                         \
-      e = cudaFuncSetAttribute(score_umma_kernel<TF, L2, PR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes); \
+      e = cudaFuncSetAttribute(score_umma_kernel<TF, L2, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes); \
       if (e == cudaSuccess) S.attr_set[vi] = true;                                                                 \
     }                                                                                                              \
-    if (e == cudaSuccess) score_umma_kernel<TF, L2, PR><<<grid, kUmThreads, kUmSmemBytes, st>>>(tmq, tmx, p);      \
+    if (e == cudaSuccess)                                                                                          \
+      score_umma_kernel<TF, L2, SP><<<grid, SP ? kUmThreadsSplit : kUmThreads, kUmSmemBytes, st>>>(tmq, tmqlo, tmx, p); \
   } while (0)
-    const bool pair = c.force_pair > 0;   // pairs lose the accumulator double-buffering: kept for experiments only
-    if (pair) {
-      if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true, true); else B2R_UM_LAUNCH(true, false, true); }
-      else     { if (c.norm2) B2R_UM_LAUNCH(false, true, true); else B2R_UM_LAUNCH(false, false, true); }
+    if (c.split) {   // 3xTF32: fp32 rows only
+      if (c.norm2) B2R_UM_LAUNCH(true, true, true); else B2R_UM_LAUNCH(true, false, true);
     } else {
       if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true, false); else B2R_UM_LAUNCH(true, false, false); }
       else     { if (c.norm2) B2R_UM_LAUNCH(false, true, false); else B2R_UM_LAUNCH(false, false, false); }
@@ -633,9 +656,13 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   // here with 2 ulp (2^-23) of the running magnitude per instruction: (d/8 + 8) * 2^-23 for bf16,
   // (d/4 + 8) * 2^-23 for tf32 (measured: 2.8e-7 at d=768, tools/umma_probe, 40x below this).  TF32 adds the
   // truncation of both operands: |trunc(a) trunc(b) - ab| <= (2^-10 + 2^-10 + 2^-20) |ab|.
-  fp.errfac = float(f32 ? (double(c.d) / 4 + 8.0) * 1.1921e-7 + 1.96e-3 : (double(c.d) / 8 + 8.0) * 1.1921e-7);
+  // 3xTF32 folds three instructions per K-slice and drops q_lo.x_lo (<= 2^-20) and the TF32 truncation of the two
+  // low parts (2 * 2^-21).
+  fp.errfac = float(c.split ? (3.0 * double(c.d) / 4 + 8.0) * 1.1921e-7 + 2.0e-6
+                    : f32   ? (double(c.d) / 4 + 8.0) * 1.1921e-7 + 1.96e-3
+                            : (double(c.d) / 8 + 8.0) * 1.1921e-7);
 
-  std::vector<CUtensorMap> tmq(nlaunch);
+  std::vector<CUtensorMap> tmq(nlaunch), tmqlo(nlaunch);
   std::vector<UmmaParams> pp(nlaunch);
   for (int l = 0; l < nlaunch; ++l) {
     const int q0 = l * kUmQMax;
@@ -645,6 +672,9 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     // boxes that stay inside the tensor avoid TMA's out-of-bounds handling on every load
     const uint64_t nq_box = uint64_t((nq + 2 * kUmBM - 1) / (2 * kUmBM)) * (2 * kUmBM);
     rc = umma_make_map(S, &tmq[l], f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), nq_box, uint64_t(c.ld) * esz, kUmBM, err);
+    if (rc) return rc;
+    const char* qlo = c.split ? reinterpret_cast<const char*>(c.Qlo) : qbase;   // unused map when not split
+    rc = umma_make_map(S, &tmqlo[l], f32, qlo + size_t(q0) * c.ld * esz, uint64_t(c.ld), nq_box, uint64_t(c.ld) * esz, kUmBM, err);
     if (rc) return rc;
     UmmaParams& p = pp[l];
     p = UmmaParams{};
@@ -656,7 +686,7 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     p.dbg = c.dbg; p.dbg_flags = c.dbg_flags;
     // seed launch
     p.row0 = 0; p.ntiles = tiles_seed; p.slot_base = 0; p.bisect_first = 1;
-    cudaError_t e = launch(grid_seed, tmq[l], p);
+    cudaError_t e = launch(grid_seed, tmq[l], tmqlo[l], p);
     if (e != cudaSuccess) { err = std::string("tcgen05 seed launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
   }
@@ -680,7 +710,7 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     for (int l = 0; l < nlaunch; ++l) {
       UmmaParams& p = pp[l];
       p.row0 = int64_t(tiles_seed) * kUmBN; p.ntiles = tiles_main; p.slot_base = grid_seed; p.bisect_first = 0;
-      e = launch(grid_main, tmq[l], p);
+      e = launch(grid_main, tmq[l], tmqlo[l], p);
       if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
       ++*launches;
     }

@@ -19,7 +19,7 @@ from typing import Tuple
 import numpy as np
 
 from . import _lib
-from ._lib import (ENGINE_AUTO, ENGINE_FMA, ENGINE_UMMA, METRIC_INNER_PRODUCT, METRIC_L2, STORE_BF16, STORE_F32,
+from ._lib import (ENGINE_AUTO, ENGINE_FMA, ENGINE_UMMA, ENGINE_UMMA3, METRIC_INNER_PRODUCT, METRIC_L2, STORE_BF16, STORE_F32,
                    B2RError, SearchStats, check)
 
 

@@ -63,8 +63,8 @@ def test_config5_shape_batch4096_bf16(oracle):
 
 
 def test_unproven_search_falls_back_and_stays_exact(oracle):
-    """60 exact copies of one row: the gap between the k-th and the K'-th candidate is zero, so the tensor-core
-    pass cannot prove completeness; the call must repeat on the FMA engine and still return the lowest ids."""
+    """60 exact copies of one row: the gap between the k-th and the K'-th candidate is zero, so the 1xTF32 pass
+    cannot prove completeness; the call must repeat with the 3xTF32 split and still return the lowest ids."""
     x, q = _data(oracle, 30_000, 256, 4, 60)
     x[1000:1060] = x[7]
     q[0] = x[7]
@@ -74,7 +74,25 @@ def test_unproven_search_falls_back_and_stays_exact(oracle):
     _check(D, I, *oracle.search_ref(x, q, 10, 0, extra=128))
     assert I[0, 0] == 7 and list(I[0, 1:]) == list(range(1000, 1009))
     st = idx.last_stats()
-    assert st["fallback"] == 1 and st["engine"] == b2r.ENGINE_FMA
+    assert st["fallback"] == 1 and st["engine"] == b2r.ENGINE_UMMA3
+
+
+@pytest.mark.parametrize("metric", [b2r.METRIC_INNER_PRODUCT, b2r.METRIC_L2])
+def test_3xtf32_engine_parity(oracle, metric):
+    """The split-TF32 variant of the tcgen05 kernel (exact mode's fallback), forced, against the oracle."""
+    x, q = _data(oracle, 50_000, 768, 150, 70)
+    idx = b2r.IndexFlat(768, metric)
+    idx.set_engine(b2r.ENGINE_UMMA3)
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    _check(D, I, *oracle.search_ref(x, q, 10, metric))
+    st = idx.last_stats()
+    assert st["engine"] == b2r.ENGINE_UMMA3 and st["unverified"] == 0 and st["kprime"] == 16
+    fast = b2r.IndexFlatIP(768, storage="bf16")
+    fast.set_engine(b2r.ENGINE_UMMA3)
+    fast.add(x[:100])
+    with pytest.raises(b2r.B2RError):                 # 3xTF32 is for fp32 rows
+        fast.search(q, 3)
 
 
 def test_full_size_properties_1m_768(oracle):

@@ -42,7 +42,7 @@ static float tf32_trunc(float f) {
   return f;
 }
 
-static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_count, unsigned seed) {
+static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_count, unsigned seed, bool split = false) {
   const int ld = (d + 63) / 64 * 64;
   srand(seed);
   std::vector<float> hx(size_t(n) * ld, 0.f), hq(size_t(nq) * ld, 0.f), hn2(n, 0.f);
@@ -84,12 +84,21 @@ static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_
     CK(cudaMemcpy(dQ, bq.data(), bq.size() * 2, cudaMemcpyHostToDevice));
   }
   CK(cudaMemcpy(dn2, hn2.data(), n * 4, cudaMemcpyHostToDevice));
+  float* dQlo = nullptr;
+  if (split) {   // q - trunc_tf32(q)
+    std::vector<float> lo(hq.size());
+    for (size_t i = 0; i < hq.size(); ++i) lo[i] = hq[i] - tf32_trunc(hq[i]);
+    CK(cudaMalloc(&dQlo, size_t(nq + 256) * ld * 4));
+    CK(cudaMemset(dQlo, 0, size_t(nq + 256) * ld * 4));
+    CK(cudaMemcpy(dQlo, lo.data(), lo.size() * 4, cudaMemcpyHostToDevice));
+  }
 
   UmmaState S;
   UmmaCall c{};
   c.X = dX; c.n = n; c.ld = ld; c.d = d; c.storage = f32 ? 0 : 1;
   c.Qh = dQ; c.Qf = reinterpret_cast<const float*>(dQ); c.nq = nq; c.kp = kp;
   c.norm2 = l2 ? dn2 : nullptr; c.thr = dthr; c.sm_count = sm_count; c.dbg = ddbg;
+  c.split = split; c.Qlo = dQlo;
   FinalizeParams fp{};
   int launches = 0;
   std::string err;
@@ -117,7 +126,7 @@ static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_
       double s = 0;
       for (int j = 0; j < d; ++j) {
         float a = hq[size_t(q) * ld + j], b = hx[r * ld + j];
-        if (f32) { a = tf32_trunc(a); b = tf32_trunc(b); }
+        if (f32 && !split) { a = tf32_trunc(a); b = tf32_trunc(b); }
         s += double(a) * b;
       }
       if (l2) s -= 0.5 * hn2[r];
@@ -128,7 +137,7 @@ static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_
       if (gu == 0xffffffffu) { ++unwritten; continue; }
       double e = fabs(double(g) - s);
       maxerr = std::max(maxerr, e);
-      if (e > (f32 ? 2e-3 : 1e-4)) {
+      if (e > (split ? 2e-5 : f32 ? 2e-3 : 1e-4)) {
         ++bad;
         if (shown < 6) { printf("    mismatch q=%d row=%lld got=%g want=%g\n", q, (long long)r, g, s); ++shown; }
       }
@@ -160,7 +169,7 @@ static int run_case(int64_t n, int nq, int d, int kp, bool f32, bool l2, int sm_
       }
   }
   printf("  n=%lld nq=%d d=%d kp=%d %s %s: %.3f ms  maxerr=%.3g bad=%lld unwritten=%lld | cand/query=%.1f maxcnt=%lld cap=%d missing=%lld %s\n",
-         (long long)n, nq, d, kp, f32 ? "tf32" : "bf16", l2 ? "L2" : "IP", ms, maxerr, (long long)bad, (long long)unwritten,
+         (long long)n, nq, d, kp, split ? "3xtf32" : f32 ? "tf32" : "bf16", l2 ? "L2" : "IP", ms, maxerr, (long long)bad, (long long)unwritten,
          double(totalc) / nq, (long long)maxcnt, cap, (long long)missing, (bad || unwritten || missing) ? "FAIL" : "ok");
   S.release();
   cudaFree(dX); cudaFree(dQ); cudaFree(dn2); cudaFree(ddbg); cudaFree(dthr);
@@ -177,7 +186,7 @@ __global__ void fill_kernel(uint32_t* p, size_t n, uint32_t seed, int f32) {
 }
 
 // perf mode: no verification, device-generated data, timing of the launch set under diagnostic flags
-static int run_perf(int64_t n, int nq, int d, bool f32, int flags, int pairmode, int sm_count) {
+static int run_perf(int64_t n, int nq, int d, bool f32, int flags, int split, int sm_count) {
   const int ld = (d + 63) / 64 * 64;
   const size_t esz = f32 ? 4 : 2;
   void *dX, *dQ; uint32_t* dthr;
@@ -190,7 +199,7 @@ static int run_perf(int64_t n, int nq, int d, bool f32, int flags, int pairmode,
   UmmaCall c{};
   c.X = dX; c.n = n; c.ld = ld; c.d = d; c.storage = f32 ? 0 : 1;
   c.Qh = dQ; c.Qf = reinterpret_cast<const float*>(dQ); c.nq = nq; c.kp = 16;
-  c.norm2 = nullptr; c.thr = dthr; c.sm_count = sm_count; c.dbg_flags = flags; c.force_pair = pairmode;
+  c.norm2 = nullptr; c.thr = dthr; c.sm_count = sm_count; c.dbg_flags = flags; c.split = split != 0 && f32; c.Qlo = reinterpret_cast<const float*>(dQ);
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   float best = 1e9f;
   for (int it = 0; it < 5; ++it) {
@@ -206,8 +215,8 @@ static int run_perf(int64_t n, int nq, int d, bool f32, int flags, int pairmode,
     best = std::min(best, ms);
   }
   const double bytes = double(n) * ld * esz, flops = 2.0 * nq * double(n) * d;
-  printf("perf n=%lld nq=%d d=%d %s flags=%d pair=%d: %.3f ms  corpus %.2f TB/s  %.0f TFLOP/s\n", (long long)n, nq, d,
-         f32 ? "tf32" : "bf16", flags, pairmode, best, bytes / best / 1e9, flops / best / 1e9);
+  printf("perf n=%lld nq=%d d=%d %s flags=%d split=%d: %.3f ms  corpus %.2f TB/s  %.0f TFLOP/s\n", (long long)n, nq, d,
+         f32 ? "tf32" : "bf16", flags, split, best, bytes / best / 1e9, flops / best / 1e9);
   S.release(); cudaFree(dX); cudaFree(dQ); cudaFree(dthr);
   return 0;
 }
@@ -223,7 +232,7 @@ int main(int argc, char** argv) {
     return run_perf(atoll(argv[2]), atoi(argv[3]), atoi(argv[4]), atoi(argv[5]) != 0, atoi(argv[6]), atoi(argv[7]), sm);
   }
   int fails = 0;
-  struct C { int64_t n; int nq, d, kp; bool f32, l2; };
+  struct C { int64_t n; int nq, d, kp; bool f32, l2; bool split = false; };
   const C cases[] = {
       {256, 128, 64, 16, false, false},     // one tile, one K step
       {256, 128, 128, 16, false, false},    // two K steps
@@ -237,12 +246,15 @@ int main(int argc, char** argv) {
       {256, 128, 32, 16, true, false},      // tf32, one K step
       {4096, 70, 384, 16, true, false},
       {20000, 33, 768, 16, true, true},
+      {256, 128, 32, 16, true, false, true},    // 3xTF32, one K step
+      {4096, 70, 384, 16, true, false, true},
+      {20000, 200, 768, 16, true, true, true},
   };
   int only = argc > 1 ? atoi(argv[1]) : -1;
   int idx = 0;
   for (const C& c : cases) {
     if (only >= 0 && idx++ != only) continue;
-    int rc = run_case(c.n, c.nq, c.d, c.kp, c.f32, c.l2, sm, 1234u + unsigned(c.n));
+    int rc = run_case(c.n, c.nq, c.d, c.kp, c.f32, c.l2, sm, 1234u + unsigned(c.n), c.split);
     if (rc == 2) { printf("aborting after a kernel fault\n"); return 2; }
     fails += rc != 0;
   }
