@@ -226,12 +226,19 @@ def main():
     sidx.local.set_engine(args.engine)
     sidx.local.reserve(hi - lo)
     chunk = 131072
+    ing0, ing1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ingest_ms = 0.0
     for r0 in range(lo, hi, chunk):
         rows = gen_rows_gpu(torch, 0, r0, min(chunk, hi - r0), DIM, device)
         b2r.normalize_L2(rows)                      # kernel (a), in place, as faiss.normalize_L2 is used
-        sidx.add_local(rows, lo, args.rows)
+        ing0.record()
+        sidx.add_local(rows, lo, args.rows)         # kernel (a) again: cast / copy into the index, row norms
+        ing1.record()
+        ing1.synchronize()
+        ingest_ms += ing0.elapsed_time(ing1)
         del rows
     torch.cuda.synchronize()
+    ingest_gbs = (hi - lo) * DIM * (4 + esize) / (ingest_ms * 1e-3) / 1e9 if ingest_ms else 0.0
 
     def make_queries(b):
         q = gen_rows_gpu(torch, 1, 0, b, DIM, device)
@@ -366,7 +373,9 @@ def main():
                     "h2d_bytes_per_step": args.batch * DIM * 4, "d2h_bytes_per_step": args.batch * args.k * 12},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roof, "cpu_baseline": cpu_base, "parity": parity, "sweep": sweep,
-            "engine": {1: "fma", 2: "umma"}.get(st["engine"], st["engine"]), "kprime": st["kprime"],
+            "engine": {1: "fma", 2: "umma", 3: "umma-3xtf32"}.get(st["engine"], st["engine"]), "kprime": st["kprime"],
+            "ingest": {"kernel": "ingest_rows_kernel", "gbs": ingest_gbs, "frac_of_hbm_peak": ingest_gbs / peaks["hbm_gbs"],
+                       "bytes_per_row": DIM * (4 + esize)},
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -418,14 +418,13 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   RC_TRY(idx->qn2.ensure(size_t(nq) * 4));
   RC_TRY(idx->thr.ensure(size_t(nq) * 4));
   RC_TRY(idx->stats.ensure(2 * sizeof(unsigned long long)));
-  CU_TRY(cudaMemsetAsync(idx->thr.p, 0, size_t(nq) * 4, st));
-  CU_TRY(cudaMemsetAsync(idx->stats.p, 0, 2 * sizeof(unsigned long long), st));
   {
     const int blocks = int(std::min<int64_t>((nq + 7) / 8, int64_t(idx->sm_count) * 8));
     prep_queries_kernel<<<blocks, 256, 0, st>>>(q_dev, nq, int(idx->d), ldq, normalize_queries,
                                                 idx->storage == B2R_STORE_BF16, static_cast<float*>(idx->qf.p),
                                                 idx->storage == B2R_STORE_BF16 ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
-                                                static_cast<float*>(idx->qn2.p), split ? static_cast<float*>(idx->qlo.p) : nullptr);
+                                                static_cast<float*>(idx->qn2.p), split ? static_cast<float*>(idx->qlo.p) : nullptr,
+                                                static_cast<uint32_t*>(idx->thr.p), static_cast<unsigned long long*>(idx->stats.p));
     CU_TRY(cudaGetLastError());
     ++launches;
   }

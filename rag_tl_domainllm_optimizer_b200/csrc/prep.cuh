@@ -140,7 +140,11 @@ __global__ void finish_maxcos_kernel(const uint32_t* __restrict__ maxord, int64_
 __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, int64_t nq, int d, int ldq,
                                                            int normalize, int round_bf16, float* __restrict__ qf,
                                                            __nv_bfloat16* __restrict__ qh, float* __restrict__ qn2,
-                                                           float* __restrict__ qlo /* optional: q - trunc_tf32(q) */) {
+                                                           float* __restrict__ qlo /* optional: q - trunc_tf32(q) */,
+                                                           uint32_t* __restrict__ thr /* [nq] cleared */,
+                                                           unsigned long long* __restrict__ stats /* [2] cleared */) {
+  // the per-search thresholds and counters start at zero: cleared here instead of by two memset launches
+  if (stats && blockIdx.x == 0 && threadIdx.x < 2) stats[threadIdx.x] = 0ull;
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
@@ -173,7 +177,10 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
       }
     }
     acc = butterfly64(acc);
-    if (lane == 0) qn2[r] = float(acc);
+    if (lane == 0) {
+      qn2[r] = float(acc);
+      if (thr) thr[r] = 0u;
+    }
   }
 }
 

@@ -49,7 +49,6 @@ __global__ void __launch_bounds__(kFmaWarps * 32, 2) score_fma_kernel(FmaParams 
   uint64_t* buf = reinterpret_cast<uint64_t*>(qs + size_t(kFmaQB) * p.ld);         // [QB][cap]
   __shared__ int cnt_s[kFmaQB];
   __shared__ float thr_s[kFmaQB];
-  __shared__ int need_s;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const T* X = reinterpret_cast<const T*>(p.X);
@@ -63,7 +62,6 @@ __global__ void __launch_bounds__(kFmaWarps * 32, 2) score_fma_kernel(FmaParams 
   }
   for (int i = tid; i < kFmaQB * p.cap; i += blockDim.x) buf[i] = 0ull;
   if (tid < kFmaQB) { cnt_s[tid] = 0; thr_s[tid] = -INFINITY; }
-  if (tid == 0) need_s = 0;
   __syncthreads();
 
   const int64_t ntiles = (p.n + kFmaTile - 1) / kFmaTile;
