@@ -355,8 +355,12 @@ extern "C" int b2r_index_set_pad(b2r_index* idx, int pad) {
 static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, FinalizeParams& fp, int* launches) {
   const int64_t ntiles = (idx->ntotal + kFmaTile - 1) / kFmaTile;
   const int grid = int(std::max<int64_t>(1, std::min<int64_t>(ntiles, int64_t(idx->sm_count) * 2)));
-  const int cap = host_next_pow2(std::max(2 * kp, kp + 2 * kFmaTile));
-  const size_t smem = size_t(kFmaQB) * idx->ld * 4 + size_t(kFmaQB) * cap * 8;
+  int cap = host_next_pow2(std::max(2 * kp, kp + 2 * kFmaTile));
+  size_t smem = size_t(kFmaQB) * idx->ld * 4 + size_t(kFmaQB) * cap * 8;
+  if (smem > 227 * 1024) {   // large k: settle for the smallest buffer that still absorbs one tile between compactions
+    cap = host_next_pow2(kp + 2 * kFmaTile);
+    smem = size_t(kFmaQB) * idx->ld * 4 + size_t(kFmaQB) * cap * 8;
+  }
   if (smem > 227 * 1024)
     return fail(B2R_ERR_LIMIT, "FMA engine needs %zu bytes of shared memory (d=%lld, k'=%d); limit is 232448", smem, (long long)idx->d, kp);
   RC_TRY(idx->cand.ensure(size_t(grid) * nq * kp * 8));

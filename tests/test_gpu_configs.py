@@ -137,3 +137,32 @@ def test_full_size_properties_1m_768(oracle):
     _, If = fast.search(q, k)
     rec = np.mean([len(set(a) & set(b)) / k for a, b in zip(If.cpu().numpy(), I)])
     assert rec >= 0.9
+
+
+@pytest.mark.parametrize("n,d,nq,k", [(1, 8, 1, 1), (33, 100, 3, 7), (300, 64, 130, 10), (4097, 260, 17, 33)])
+def test_bf16_ragged_small_shapes(oracle, n, d, nq, k):
+    """Fast mode on the tcgen05 engine with fewer rows than a tile, ragged d, more than one query tile."""
+    rng = np.random.default_rng(n + d)
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    q = rng.standard_normal((nq, d)).astype(np.float32)
+    for metric in (b2r.METRIC_INNER_PRODUCT, b2r.METRIC_L2):
+        idx = b2r.IndexFlat(d, metric, storage="bf16")
+        idx.add(x)
+        D, I = idx.search(q, k)
+        _check(D, I, *oracle.search_defined(oracle.round_bf16(x), oracle.round_bf16(q), k, metric))
+        assert idx.last_stats()["engine"] == b2r.ENGINE_UMMA
+
+
+def test_maximum_k(oracle):
+    """k = 1024 (the documented maximum) goes through the FMA engine; k = 128 is the largest exact-mode k on tcgen05."""
+    x, q = _data(oracle, 6000, 128, 5, 80)
+    idx = b2r.IndexFlatIP(128)
+    idx.add(x)
+    D, I = idx.search(q, 1024)
+    _check(D, I, *oracle.search_defined(x, q, 1024, 0))
+    assert idx.last_stats()["engine"] == b2r.ENGINE_FMA
+    D, I = idx.search(q, 128)
+    _check(D, I, *oracle.search_defined(x, q, 128, 0))
+    assert idx.last_stats()["engine"] in (b2r.ENGINE_UMMA, b2r.ENGINE_UMMA3)
+    with pytest.raises(b2r.B2RError):
+        idx.search(q, 1025)
