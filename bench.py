@@ -157,7 +157,8 @@ def run_reference(args, rank, world):
 def workload_config(args, world):
     return {"workload": f"{'configs[1]: ' if (args.rows, DIM) == (N_ROWS, 768) else ''}{args.rows}x{DIM} corpus, query batch {args.batch}, k={args.k}, "
                         f"{'exact fp32' if args.mode == 'exact' else 'bf16'} inner-product flat search",
-            "rows": args.rows, "dim": DIM, "batch": args.batch, "k": args.k, "mode": args.mode,
+            "rows": args.rows, "dim": DIM, "batch": args.batch, "k": args.k,
+            "mode": args.mode + ("+bf16-shadow prefilter" if getattr(args, "shadow", False) and args.mode == "exact" else ""),
             "sharding": f"rows/{world}" if world > 1 else "none",
             "l2": "inputs larger than L2: corpus shard re-read from HBM every step (>= 126 MB)"}
 
@@ -175,6 +176,7 @@ def main():
     ap.add_argument("--dim", type=int, default=DIM, help="embedding dimension (other BASELINE configs)")
     ap.add_argument("--mode", default="exact", choices=["exact", "bf16"])
     ap.add_argument("--engine", type=int, default=0)
+    ap.add_argument("--shadow", action="store_true", help="exact mode: score a bf16 shadow copy, re-score fp32 rows")
     ap.add_argument("--sweep", default="1,8,32,128,1024", help="comma list of extra batch sizes ('' = none)")
     ap.add_argument("--cpu-queries", type=int, default=256)
     ap.add_argument("--no-cpu", action="store_true")
@@ -219,10 +221,12 @@ def main():
     peaks, peak_src = load_peaks()
     storage = "f32" if args.mode == "exact" else "bf16"
     esize = 4 if storage == "f32" else 2
+    esize_score = 2 if (args.shadow and storage == "f32") else esize   # bytes per element the scoring pass reads
 
     # ---- corpus shard + queries -------------------------------------------------------------
     lo, hi = b2r.shard_bounds(args.rows, world, rank)
-    sidx = b2r.ShardedIndexFlat(DIM, b2r.METRIC_INNER_PRODUCT, storage=storage, device=local_rank)
+    sidx = b2r.ShardedIndexFlat(DIM, b2r.METRIC_INNER_PRODUCT, storage=storage, device=local_rank,
+                                shadow=args.shadow and storage == "f32")
     sidx.local.set_engine(args.engine)
     sidx.local.reserve(hi - lo)
     chunk = 131072
@@ -291,7 +295,7 @@ def main():
     # ---- roofline of the dominant (scoring) kernel -------------------------------------------
     n_local = hi - lo
     rows_k = (st["main_rows"] or n_local) if st["engine"] == 2 else n_local    # rows the timed (dominant) launch covers
-    bytes_alg = rows_k * DIM * esize
+    bytes_alg = rows_k * DIM * esize_score
     flops_alg = 2.0 * args.batch * rows_k * DIM
     hbm_gbs = bytes_alg / (score_ms * 1e-3) / 1e9 if score_ms else 0.0
     tflops = flops_alg / (score_ms * 1e-3) / 1e12 if score_ms else 0.0
@@ -306,7 +310,7 @@ def main():
     else:
         roof = {"bound": "tensor", "achieved": tflops, "peak": tc_peak, "unit": "TFLOP/s", "frac": tc_frac,
                 "frac_of_sustained_peak": tflops / tc_sustained}
-    if storage == "f32" and st["engine"] == 2:
+    if storage == "f32" and st["engine"] in (2, 3):
         # exact mode runs kind::tf32 MMAs, whose dense rate is half the bf16 rate (1.1 vs 2.25 PFLOP/s nominal);
         # MEASURED_PEAKS.json has no tf32 figure, so the fraction against half the measured bf16 peak is added
         roof["frac_of_tf32_peak_derived"] = tflops / (tc_peak / 2.0)
@@ -367,13 +371,13 @@ def main():
             "metric": "flat top-k search queries/sec", "value": qps, "unit": "queries/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None,
-            "dtype": ("tf32" if st["engine"] == 2 else "f32") if storage == "f32" else "bf16",
+            "dtype": {2: "tf32", 3: "tf32", 4: "bf16"}.get(st["engine"], "f32") if storage == "f32" else "bf16",
             "data": "synthetic", "config": workload_config(args, world), "clocks": clocks,
             "e2e": {"value": e2e_qps, "unit": "queries/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": args.batch * DIM * 4, "d2h_bytes_per_step": args.batch * args.k * 12},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roof, "cpu_baseline": cpu_base, "parity": parity, "sweep": sweep,
-            "engine": {1: "fma", 2: "umma", 3: "umma-3xtf32"}.get(st["engine"], st["engine"]), "kprime": st["kprime"],
+            "engine": {1: "fma", 2: "umma", 3: "umma-3xtf32", 4: "umma-bf16-shadow"}.get(st["engine"], st["engine"]), "kprime": st["kprime"],
             "ingest": {"kernel": "ingest_rows_kernel", "gbs": ingest_gbs, "frac_of_hbm_peak": ingest_gbs / peaks["hbm_gbs"],
                        "bytes_per_row": DIM * (4 + esize)},
         }

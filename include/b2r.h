@@ -62,8 +62,10 @@ enum {
   B2R_ENGINE_FMA = 1,   /* CUDA-core fp32 FMA streaming kernel                        */
   B2R_ENGINE_UMMA = 2,  /* TMA + tcgen05.mma + TMEM kernel: kind::f16 on bf16 rows,   */
                         /* one kind::tf32 pass on fp32 rows                           */
-  B2R_ENGINE_UMMA3 = 3  /* the same kernel with the 3xTF32 split (fp32 rows): the     */
+  B2R_ENGINE_UMMA3 = 3, /* the same kernel with the 3xTF32 split (fp32 rows): the     */
                         /* fallback of exact mode when the 1xTF32 proof fails         */
+  B2R_ENGINE_SHADOW = 4 /* reported only: kind::f16 on the bf16 shadow of fp32 rows   */
+                        /* (b2r_index_set_shadow), exact re-scoring on the fp32 rows  */
 };
 
 /* Counters of the most recent search on a handle (b2r_index_last_stats). */
@@ -174,6 +176,11 @@ int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k,
 
 /* Force a scoring engine (B2R_ENGINE_*); AUTO picks per call. */
 int b2r_index_set_engine(b2r_index* idx, int engine);
+
+/* Exact mode only, before the first add: also keep a bf16 copy of the rows (+50 % memory) and let the
+ * scoring pass run on it — half the HBM bytes and twice the MMA rate of the TF32 pass; results stay
+ * those of exact mode (fp32 rows are re-scored, the proof and its fallback apply).  No faiss counterpart. */
+int b2r_index_set_shadow(b2r_index* idx, int on);
 
 /* Extra candidates kept per query before the exact re-scoring (default 6). */
 int b2r_index_set_pad(b2r_index* idx, int pad);

@@ -132,6 +132,8 @@ struct b2r_index {
   int ld = 0;             // row pitch in elements (multiple of 64: one 128-byte TMA/UMMA swizzle row in bf16, two in fp32)
   int64_t ntotal = 0, cap_rows = 0;
   void* X = nullptr;      // [cap_rows][ld] fp32 or bf16
+  void* Xs = nullptr;     // optional bf16 shadow of fp32 rows, same pitch (b2r_index_set_shadow)
+  bool shadow = false;
   float* norm2 = nullptr; // [cap_rows] squared norm of the stored rows (L2 metric only)
   float* maxnorm2 = nullptr;  // device scalar: largest stored squared norm
   int sm_count = 148;
@@ -192,6 +194,7 @@ extern "C" void b2r_index_free(b2r_index* idx) {
   DeviceGuard g(idx->device);
   cudaDeviceSynchronize();
   if (idx->X) cudaFree(idx->X);
+  if (idx->Xs) cudaFree(idx->Xs);
   if (idx->norm2) cudaFree(idx->norm2);
   if (idx->maxnorm2) cudaFree(idx->maxnorm2);
   if (idx->host_flag) cudaFreeHost(idx->host_flag);
@@ -231,14 +234,27 @@ static int grow(b2r_index* idx, int64_t rows, cudaStream_t st) {
       return fail(B2R_ERR_OOM, "cannot allocate row norms for %lld rows", (long long)want);
     }
   }
+  void* ns = nullptr;
+  if (idx->shadow) {
+    e = cudaMalloc(&ns, size_t(want) * idx->ld * 2);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      cudaFree(nx);
+      if (nn) cudaFree(nn);
+      return fail(B2R_ERR_OOM, "cannot allocate the bf16 shadow for %lld rows", (long long)want);
+    }
+    if (idx->ntotal > 0) CU_TRY(cudaMemcpyAsync(ns, idx->Xs, size_t(idx->ntotal) * idx->ld * 2, cudaMemcpyDeviceToDevice, st));
+  }
   if (idx->ntotal > 0) {
     CU_TRY(cudaMemcpyAsync(nx, idx->X, size_t(idx->ntotal) * rowb, cudaMemcpyDeviceToDevice, st));
     if (nn) CU_TRY(cudaMemcpyAsync(nn, idx->norm2, size_t(idx->ntotal) * sizeof(float), cudaMemcpyDeviceToDevice, st));
     CU_TRY(cudaStreamSynchronize(st));
   }
   if (idx->X) cudaFree(idx->X);
+  if (idx->Xs) cudaFree(idx->Xs);
   if (idx->norm2) cudaFree(idx->norm2);
   idx->X = nx;
+  idx->Xs = ns;
   idx->norm2 = nn;
   idx->cap_rows = want;
   idx->umma.invalidate();
@@ -282,6 +298,8 @@ extern "C" int b2r_index_add(b2r_index* idx, int64_t n, const float* x, int norm
     } else {
       float* dst = static_cast<float*>(idx->X) + row0 * idx->ld;
       ingest_rows_kernel<float><<<blocks, 256, 0, st>>>(src, m, int(idx->d), dst, idx->ld, normalize, n2, idx->maxnorm2);
+      if (idx->shadow)
+        shadow_rows_kernel<<<blocks, 256, 0, st>>>(dst, m, idx->ld, static_cast<__nv_bfloat16*>(idx->Xs) + row0 * idx->ld);
     }
     CU_TRY(cudaGetLastError());
     if (!dev_in) CU_TRY(cudaStreamSynchronize(st));  // the staging buffer is reused by the next chunk
@@ -339,6 +357,14 @@ extern "C" int b2r_index_set_engine(b2r_index* idx, int engine) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
   if (engine < B2R_ENGINE_AUTO || engine > B2R_ENGINE_UMMA3) return fail(B2R_ERR_ARG, "unknown engine %d", engine);
   idx->engine = engine;
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_set_shadow(b2r_index* idx, int on) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (idx->storage != B2R_STORE_F32) return fail(B2R_ERR_ARG, "a bf16 shadow only makes sense for fp32 rows (exact mode)");
+  if (idx->ntotal != 0 || idx->cap_rows != 0) return fail(B2R_ERR_STATE, "set the shadow option before the first add/reserve");
+  idx->shadow = on != 0;
   return B2R_OK;
 }
 
@@ -401,18 +427,22 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   // candidate list (K' >= 2k, at least k + 22) for the completeness proof to go through; FMA, bf16 (exact
   // products) and 3xTF32 keep k + pad.  The pad grows with k: gaps between neighbouring scores shrink like 1/rank.
   const int engine = force_engine ? force_engine : idx->engine;
-  bool use_umma = false, split = false;
+  bool use_umma = false, split = false, use_shadow = false;
   int kp = int(std::min<int64_t>(k + std::max<int64_t>(idx->pad, k / 8), 2048));
   if (idx->ntotal > 0 && engine != B2R_ENGINE_FMA) {
     split = engine == B2R_ENGINE_UMMA3;
     if (split && idx->storage != B2R_STORE_F32)
       return fail(B2R_ERR_ARG, "the 3xTF32 engine needs fp32 rows (exact mode)");
-    const int kp_tc = (idx->storage == B2R_STORE_F32 && !split) ? int(k + std::max<int64_t>(std::max(idx->pad, 22), k)) : kp;
+    // exact mode with a bf16 shadow: score the shadow (half the bytes, twice the MMA rate); rounding both operands
+    // to bf16 costs 2^-8 relative, twice the TF32 truncation, hence a slightly wider K'
+    use_shadow = idx->shadow && idx->storage == B2R_STORE_F32 && !split && engine == B2R_ENGINE_AUTO;
+    const int kp_tc = (idx->storage == B2R_STORE_F32 && !split)
+                          ? int(k + std::max<int64_t>(std::max(idx->pad, use_shadow ? 30 : 22), k)) : kp;
     use_umma = umma_supported(idx->storage, int(idx->d), kp_tc, idx->ntotal);
     if (use_umma) kp = kp_tc;
     else if (engine == B2R_ENGINE_UMMA || engine == B2R_ENGINE_UMMA3)
       return fail(B2R_ERR_LIMIT, "the tcgen05 engine does not take this shape (storage %d, d %lld, k' %d)", idx->storage, (long long)idx->d, kp_tc);
-    if (!use_umma) split = false;
+    if (!use_umma) { split = false; use_shadow = false; }
   }
   int launches = 0;
   const int ldq = idx->ld;
@@ -426,7 +456,7 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
     const int blocks = int(std::min<int64_t>((nq + 7) / 8, int64_t(idx->sm_count) * 8));
     prep_queries_kernel<<<blocks, 256, 0, st>>>(q_dev, nq, int(idx->d), ldq, normalize_queries,
                                                 idx->storage == B2R_STORE_BF16, static_cast<float*>(idx->qf.p),
-                                                idx->storage == B2R_STORE_BF16 ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
+                                                (idx->storage == B2R_STORE_BF16 || use_shadow) ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
                                                 static_cast<float*>(idx->qn2.p), split ? static_cast<float*>(idx->qlo.p) : nullptr,
                                                 static_cast<uint32_t*>(idx->thr.p), static_cast<unsigned long long*>(idx->stats.p));
     CU_TRY(cudaGetLastError());
@@ -440,7 +470,9 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
     if (!use_umma) CU_TRY(cudaEventRecord(idx->ev0[slot], st));
     if (use_umma) {
       UmmaCall uc{};
-      uc.X = idx->X; uc.n = idx->ntotal; uc.ld = idx->ld; uc.d = int(idx->d); uc.storage = idx->storage;
+      uc.X = use_shadow ? idx->Xs : idx->X; uc.n = idx->ntotal; uc.ld = idx->ld; uc.d = int(idx->d);
+      uc.storage = use_shadow ? B2R_STORE_BF16 : idx->storage;
+      uc.shadow = use_shadow;
       uc.Qh = idx->qh.p; uc.Qf = static_cast<const float*>(idx->qf.p); uc.nq = int(nq); uc.kp = kp;
       uc.norm2 = idx->metric == B2R_METRIC_L2 ? idx->norm2 : nullptr;
       uc.thr = static_cast<uint32_t*>(idx->thr.p);
@@ -450,7 +482,7 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
       std::string err;
       int rc = umma_launch(idx->umma, uc, st, fp, &launches, err);
       if (rc != B2R_OK) return fail(rc, "%s", err.c_str());
-      engine_used = split ? B2R_ENGINE_UMMA3 : B2R_ENGINE_UMMA;
+      engine_used = split ? B2R_ENGINE_UMMA3 : use_shadow ? B2R_ENGINE_SHADOW : B2R_ENGINE_UMMA;
       main_rows = uc.main_rows;
       if (main_rows == 0) {   // tiny index: everything ran in the seed launch; nothing to time separately
         CU_TRY(cudaEventRecord(idx->ev0[slot], st));
@@ -528,7 +560,7 @@ static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int
   }
   RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, 0));
   idx->last.fallback = 0;
-  if (idx->last.engine == B2R_ENGINE_UMMA && idx->storage == B2R_STORE_F32 && idx->verify) {
+  if ((idx->last.engine == B2R_ENGINE_UMMA || idx->last.engine == B2R_ENGINE_SHADOW) && idx->storage == B2R_STORE_F32 && idx->verify) {
     // exact mode on the tensor cores is only as good as its proof: read the counter of unproven queries and, if
     // any, search again with the 3xTF32 split (error bound ~30x tighter; FMA engine where tcgen05 cannot take the
     // shape).  Costs one stream sync per search.
@@ -812,6 +844,9 @@ extern "C" int b2r_index_import_rows(b2r_index* idx, int64_t n, const void* rows
     row_norms_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dst), n, int(idx->d), idx->ld, n2, idx->maxnorm2);
   else
     row_norms_kernel<float><<<blocks, 256, 0, st>>>(reinterpret_cast<const float*>(dst), n, int(idx->d), idx->ld, n2, idx->maxnorm2);
+  if (idx->shadow)
+    shadow_rows_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const float*>(dst), n, idx->ld,
+                                               static_cast<__nv_bfloat16*>(idx->Xs) + idx->ntotal * idx->ld);
   CU_TRY(cudaGetLastError());
   if (!is_device_ptr(rows)) CU_TRY(cudaStreamSynchronize(st));   // the caller may reuse its host buffer
   idx->ntotal += n;

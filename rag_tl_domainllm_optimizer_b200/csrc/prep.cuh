@@ -203,4 +203,11 @@ __global__ void __launch_bounds__(256) row_norms_kernel(const T* __restrict__ X,
   }
   if (maxnorm2 && lane == 0 && wmax > 0.f) atomicMax(reinterpret_cast<int*>(maxnorm2), __float_as_int(wmax));
 }
+// bf16 shadow of stored fp32 rows (exact mode's optional prefilter copy): same pitch, RN-even.
+__global__ void __launch_bounds__(256) shadow_rows_kernel(const float* __restrict__ X, int64_t n, int ld,
+                                                          __nv_bfloat16* __restrict__ Xs) {
+  const int64_t total = n * int64_t(ld / 4);
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += int64_t(gridDim.x) * blockDim.x)
+    st4(Xs + i * 4, ld4(X + i * 4));
+}
 }  // namespace b2r

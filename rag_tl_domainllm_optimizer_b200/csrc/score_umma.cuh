@@ -516,6 +516,7 @@ struct UmmaCall {
   const float* norm2; uint32_t* thr; int sm_count;
   float* dbg = nullptr;
   int dbg_flags = 0;
+  bool shadow = false;           // X is the bf16 shadow of fp32 rows: operands carry a 2^-9 rounding each
   bool split = false;            // 3xTF32 (fp32 rows): needs Qlo
   const float* Qlo = nullptr;    // q - trunc_tf32(q), same layout as Qf
   cudaEvent_t ev_main0 = nullptr, ev_main1 = nullptr;   // optional: recorded around the main launch(es)
@@ -660,7 +661,7 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   // low parts (2 * 2^-21).
   fp.errfac = float(c.split ? (3.0 * double(c.d) / 4 + 8.0) * 1.1921e-7 + 2.0e-6
                     : f32   ? (double(c.d) / 4 + 8.0) * 1.1921e-7 + 1.96e-3
-                            : (double(c.d) / 8 + 8.0) * 1.1921e-7);
+                            : (double(c.d) / 8 + 8.0) * 1.1921e-7 + (c.shadow ? 3.92e-3 : 0.0));
 
   std::vector<CUtensorMap> tmq(nlaunch), tmqlo(nlaunch);
   std::vector<UmmaParams> pp(nlaunch);

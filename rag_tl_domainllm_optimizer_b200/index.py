@@ -61,7 +61,7 @@ class IndexFlat:
     """Exact brute-force index.  ``storage='f32'`` is the exact mode, ``'bf16'`` the fast mode."""
 
     def __init__(self, d: int, metric: int = METRIC_L2, *, storage: str = "f32", device: int | None = None,
-                 normalize: bool = False):
+                 normalize: bool = False, shadow: bool = False):
         if int(d) <= 0:
             raise ShapeError(f"d must be positive, got {d}")
         if storage not in ("f32", "bf16"):
@@ -84,6 +84,9 @@ class IndexFlat:
         L = _lib.lib()
         check(L.b2r_index_create(ctypes.byref(self._h), self.d, self.metric_type,
                                  STORE_BF16 if storage == "bf16" else STORE_F32, self.device))
+        self.shadow = bool(shadow)       # exact mode: score a bf16 copy of the rows, re-score the fp32 rows
+        if self.shadow:
+            check(L.b2r_index_set_shadow(self._h, 1))
 
     # -- life cycle -------------------------------------------------------------------------
     def __del__(self):

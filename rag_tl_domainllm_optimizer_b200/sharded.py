@@ -25,14 +25,14 @@ class ShardedIndexFlat:
     """Every rank constructs it, adds ITS rows (``add_local``) and calls ``search`` with the same queries."""
 
     def __init__(self, d: int, metric: int = METRIC_INNER_PRODUCT, *, storage: str = "f32", device: int | None = None,
-                 normalize: bool = False, group=None, _local=None, _merge=None):
+                 normalize: bool = False, shadow: bool = False, group=None, _local=None, _merge=None):
         import torch.distributed as dist
         self._dist = dist
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         # _local / _merge let the CPU (gloo) tests stand in for the device kernels; product code never sets them
-        self.local = _local if _local is not None else IndexFlat(d, metric, storage=storage, device=device, normalize=normalize)
+        self.local = _local if _local is not None else IndexFlat(d, metric, storage=storage, device=device, normalize=normalize, shadow=shadow)
         self._merge = _merge if _merge is not None else merge_packed
         self.d, self.metric_type = d, metric
         self.row_offset = 0

@@ -166,3 +166,24 @@ def test_maximum_k(oracle):
     assert idx.last_stats()["engine"] in (b2r.ENGINE_UMMA, b2r.ENGINE_UMMA3)
     with pytest.raises(b2r.B2RError):
         idx.search(q, 1025)
+
+
+@pytest.mark.parametrize("metric", [b2r.METRIC_INNER_PRODUCT, b2r.METRIC_L2])
+def test_exact_mode_with_bf16_shadow(oracle, metric):
+    """Exact mode scoring a bf16 shadow copy: same bits as plain exact mode (fp32 rows are re-scored)."""
+    x, q = _data(oracle, 80_000, 768, 40, 90)
+    x[5000:5040] = x[11]                       # a tie cluster: forces the proof to fail for query 0
+    q[0] = x[11]
+    idx = b2r.IndexFlat(768, metric, shadow=True)
+    idx.add(x[:50_000])
+    idx.add(x[50_000:])                        # growth carries the shadow along
+    D, I = idx.search(q[1:], 10)
+    _check(D, I, *oracle.search_ref(x, q[1:], 10, metric))
+    st = idx.last_stats()
+    assert st["engine"] == b2r.ENGINE_SHADOW and st["unverified"] == 0 and st["fallback"] == 0
+    D, I = idx.search(q, 10)                    # with the tie cluster: falls back, still exact
+    _check(D, I, *oracle.search_ref(x, q, 10, metric, extra=128))
+    assert idx.last_stats()["fallback"] == 1
+    assert np.array_equal(idx.reconstruct(77), x[77])
+    with pytest.raises(b2r.B2RError):
+        b2r.IndexFlatIP(64, storage="bf16", shadow=True)
