@@ -582,7 +582,8 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   const int64_t seed_want = std::max<int64_t>(32, std::min<int64_t>(c.sm_count, ntiles / 64));
   const int mt_all = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
   const int seed_cap = mt_all > 1 ? c.sm_count - (c.sm_count - 1) % mt_all : c.sm_count;   // see grid_seed below
-  const int tiles_seed = int(std::min<int64_t>(std::min<int64_t>(ntiles, seed_want), seed_cap));
+  // a corpus of at most one tile per CTA is finished by the seed launch alone (no select, no main launch)
+  const int tiles_seed = ntiles <= seed_cap ? int(ntiles) : int(std::min<int64_t>(seed_want, seed_cap));
   const int64_t tiles_main = ntiles - tiles_seed;
   // CTAs: the (tile, query tile) items of a launch are spread over up to one CTA per SM
   // seed grid: with round-robin items CTA b visits query tile (b + j*grid) % mt on its j-th item; a grid size that
