@@ -560,10 +560,22 @@ static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int
   }
   RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, 0));
   idx->last.fallback = 0;
-  if ((idx->last.engine == B2R_ENGINE_UMMA || idx->last.engine == B2R_ENGINE_SHADOW) && idx->storage == B2R_STORE_F32 && idx->verify) {
+  const bool host_out = !packed && !out_dev;
+  auto copy_back = [&]() -> int {   // results (and the proof counter) to the host, one sync
+    if (host_out) {
+      CU_TRY(cudaMemcpyAsync(D, Dd, size_t(nq) * k * 4, cudaMemcpyDeviceToHost, st));
+      CU_TRY(cudaMemcpyAsync(I, Id, size_t(nq) * k * 8, cudaMemcpyDeviceToHost, st));
+    }
+    return B2R_OK;
+  };
+  const bool check_proof = (idx->last.engine == B2R_ENGINE_UMMA || idx->last.engine == B2R_ENGINE_SHADOW) &&
+                           idx->storage == B2R_STORE_F32 && idx->verify;
+  if (check_proof) {
     // exact mode on the tensor cores is only as good as its proof: read the counter of unproven queries and, if
     // any, search again with the 3xTF32 split (error bound ~30x tighter; FMA engine where tcgen05 cannot take the
-    // shape).  Costs one stream sync per search.
+    // shape).  Host-buffer callers pay nothing extra (the counter rides with the results); device-pointer callers
+    // pay one stream sync per search.
+    RC_TRY(copy_back());
     CU_TRY(cudaMemcpyAsync(idx->host_flag, idx->stats.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
     if (*idx->host_flag != 0ull) {
@@ -573,14 +585,12 @@ static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int
       RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, fb));
       idx->last.fallback = 1;
       idx->last.launches += l0;
+      RC_TRY(copy_back());
+      if (host_out || !q_dev) CU_TRY(cudaStreamSynchronize(st));
     }
-  }
-  if (!packed && !out_dev) {
-    CU_TRY(cudaMemcpyAsync(D, Dd, size_t(nq) * k * 4, cudaMemcpyDeviceToHost, st));
-    CU_TRY(cudaMemcpyAsync(I, Id, size_t(nq) * k * 8, cudaMemcpyDeviceToHost, st));
-    CU_TRY(cudaStreamSynchronize(st));
-  } else if (!q_dev) {
-    CU_TRY(cudaStreamSynchronize(st));  // the caller may reuse its host query buffer
+  } else {
+    RC_TRY(copy_back());
+    if (host_out || !q_dev) CU_TRY(cudaStreamSynchronize(st));   // results in host memory / host query buffer reusable
   }
   return B2R_OK;
 }
