@@ -182,6 +182,12 @@ int b2r_index_set_engine(b2r_index* idx, int engine);
  * those of exact mode (fp32 rows are re-scored, the proof and its fallback apply).  No faiss counterpart. */
 int b2r_index_set_shadow(b2r_index* idx, int on);
 
+/* Exact mode reads its proof counter after every tensor-core search and repeats unproven searches
+ * with the 3xTF32 variant (default on; costs device-pointer callers one stream sync per search).
+ * Turn it off to keep device-pointer searches fully asynchronous (e.g. under stream capture): the
+ * counter is still kept (b2r_index_last_stats: `unverified`), the fallback becomes the caller's call. */
+int b2r_index_set_verify(b2r_index* idx, int on);
+
 /* Extra candidates kept per query before the exact re-scoring (default 6). */
 int b2r_index_set_pad(b2r_index* idx, int pad);
 

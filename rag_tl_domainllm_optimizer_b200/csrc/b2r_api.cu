@@ -368,6 +368,12 @@ extern "C" int b2r_index_set_shadow(b2r_index* idx, int on) {
   return B2R_OK;
 }
 
+extern "C" int b2r_index_set_verify(b2r_index* idx, int on) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  idx->verify = on != 0;
+  return B2R_OK;
+}
+
 extern "C" int b2r_index_set_pad(b2r_index* idx, int pad) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
   if (pad < 0 || pad > 512) return fail(B2R_ERR_ARG, "pad %d out of range (0..512)", pad);

@@ -160,6 +160,10 @@ class IndexFlat:
     def set_engine(self, engine: int) -> None:
         check(_lib.lib().b2r_index_set_engine(self._h, int(engine)))
 
+    def set_verify(self, on: bool) -> None:
+        """Exact mode: proof read-back + fallback after each search (default on; off keeps searches asynchronous)."""
+        check(_lib.lib().b2r_index_set_verify(self._h, int(bool(on))))
+
     def set_pad(self, pad: int) -> None:
         check(_lib.lib().b2r_index_set_pad(self._h, int(pad)))
 
