@@ -1,10 +1,10 @@
 // finalize.cuh — kernel (c): block/grid-level top-k merge, fused with the exact re-scoring.
 //
-// One CTA (1024 threads) per query:
+// One CTA per query (1024 threads for few queries, 256 for many):
 //   1. gathers the query's candidate keys from every slot (one slot per scoring CTA) — only the valid entries,
 //      located through a prefix sum of the per-slot counts — drops everything below the final grid-wide
-//      threshold and keeps the best K' with shared-memory bitonic sorts sized to what survived
-//      (no candidate list is ever written back to HBM);
+//      threshold and keeps the best K' — radix select (8 passes of 8-bit digits) when many survive, then a
+//      bitonic sort of just those (no candidate list is ever written back to HBM);
 //   2. re-scores the K' survivors with the DOT64 arithmetic that defines the returned score
 //      (one warp per candidate row, fp64 fixed-order reduction of the stored row);
 //   3. sorts them by (fp32 score best-first, id ascending) and writes D/I (or packed keys for

@@ -1,25 +1,28 @@
 // score_umma.cuh — kernel (b), tensor-core variant: TMA -> shared memory -> tcgen05.mma -> TMEM ->
 // threshold-filtered running top-K' in the epilogue.  The [B,N] score matrix never reaches HBM.
 //
-// One persistent CTA per SM, 6 warps:
+// One persistent CTA per SM, 6 warps (10 in the 3xTF32 variant):
 //   warp 0      TMA producer   : per K-step one 128-row query box (A) and one 256-row corpus box (B),
 //                                128 bytes of K per row, SWIZZLE_128B, 4-stage mbarrier ring
 //   warp 1      MMA issuer     : one elected lane issues 4 x tcgen05.mma (M=128, N=256, 32 B of K each) per
 //                                stage into one of two 256-column TMEM accumulators; tcgen05.commit frees
 //                                the smem stage and, after the last K-step, hands the accumulator over
-//   warps 2..5  epilogue       : thread = one query (TMEM lane), tcgen05.ld 32 columns at a time; a score
-//                                is kept only if it beats the query's running threshold (>99% fail this one
-//                                compare); survivors are appended to the (CTA, query) candidate buffer.
-// Tile (m, n) = queries [128m, 128m+128) x corpus rows [256n, 256n+256); a CTA owns a contiguous range of n
-// and loops m inside it (corpus re-reads of the inner loop hit L2).
+//   warps 2..5  epilogue       : thread = one query (TMEM lane), tcgen05.ld 32 columns at a time, branch-free
+//                                pass mask against the query's running threshold (>99.9% of scores fail), then a
+//                                warp-uniform walk over the few set bits; survivors are appended to the
+//                                (CTA, query) candidate buffer
+//   warps 6..9  splitter       : 3xTF32 only: x_lo = x - trunc_tf32(x) on every landed corpus stage
+// Work item (t, m) = corpus rows [256t, 256t+256) x queries [128m, 128m+128), t-major, dealt round-robin to the
+// CTAs so that the re-reads of a corpus tile by the other query tiles hit L2.
 //
 // Running top-K': threshold + append buffer (cap entries per (CTA, query), interleaved [entry][lane] so that a
-// warp's accesses coalesce).  First tile of a query: the threshold is found by bisection over the 256 scores
-// while they still sit in TMEM (no memory traffic).  When a buffer is nearly full the owning lane selects a
-// new threshold by bisection on the packed keys (lane-parallel: all lanes of a warp compact their own buffers
-// at once), keeps [K', kmax] entries and publishes the bound with a global atomicMax, so all 148 CTAs filter
-// with the best bound any of them has found.  A published bound is always the K'-th best score of a real
-// subset of rows, hence a valid lower bound of the final K'-th best.
+// warp's accesses coalesce).  Thresholds are SEEDED: a first launch of this kernel covers the first S rows, one
+// seed tile per (CTA, query tile), and finds each query's threshold by bisection over the 256 scores while they
+// still sit in TMEM (no memory traffic); seed_select_kernel turns the seed candidates into the exact K'-th best
+// of those rows; the main launch filters with it.  When a buffer is nearly full the owning lane selects a new
+// threshold by bisection on the packed keys (lane-parallel), keeps [K', kmax] entries and publishes the bound
+// with a global atomicMax, so all CTAs filter with the best bound any of them has found.  A published bound is
+// always the K'-th best score of a real subset of rows, hence a valid lower bound of the final K'-th best.
 //
 // Algorithmic HBM bytes per search: rows * ld * sizeof(elem) (the corpus shard, once).
 // Algorithmic flops: 2 * nq * rows * d.
