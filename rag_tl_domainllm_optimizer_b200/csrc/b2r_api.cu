@@ -509,7 +509,7 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   fp.nq = int(nq); fp.kp = kp; fp.k = int(k);
   // few queries: one big CTA per query (latency); many queries: small CTAs, several per SM (throughput)
   const int fin_threads = nq >= 256 ? 256 : kFinThreads;
-  fp.sortn = std::max(4096, host_next_pow2(kp + fin_threads));
+  fp.sortn = std::max(4096, host_next_pow2(kp + 2048));   // gather rounds append up to 2048 keys
   fp.X = idx->X; fp.ld = idx->ld; fp.d = int(idx->d); fp.storage = idx->storage;
   fp.Q = static_cast<const float*>(idx->qf.p); fp.ldq = ldq; fp.qn2 = static_cast<const float*>(idx->qn2.p);
   fp.metric = idx->metric; fp.n = idx->ntotal; fp.row_offset = row_offset;
@@ -626,7 +626,7 @@ extern "C" int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k, co
   DeviceGuard g(device);
   if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int sortn = std::max(2048, host_next_pow2(int(2 * k)));
+  const int sortn = std::max(4096, host_next_pow2(int(k) + 2048));   // gather rounds append up to 2048 keys
   merge_packed_kernel<<<int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st>>>(packed, int(G), int(nq), int(k), sortn, metric, D, I);
   CU_TRY(cudaGetLastError());
   return B2R_OK;

@@ -95,7 +95,22 @@ __device__ __forceinline__ double fold1(double acc, float a, float b) {
 template <Red R, typename TA, typename TB>
 __device__ __forceinline__ double warp_reduce64(const TA* a, const TB* b, int d, int lane) {
   double acc = 0.0;
-  for (int c = lane * 4; c < d; c += 128) {
+  int c = lane * 4;
+  // four chunks per trip: the eight loads are issued before the first fold (rows come from HBM at random
+  // addresses; one load in flight per trip made the re-scoring latency-bound).  Same fold order as the plain loop.
+  for (; c + 3 * 128 + 4 <= d; c += 4 * 128) {
+    float4 va[4], vb[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { va[u] = ld4(a + c + u * 128); vb[u] = ld4(b + c + u * 128); }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      acc = fold1<R>(acc, va[u].x, vb[u].x);
+      acc = fold1<R>(acc, va[u].y, vb[u].y);
+      acc = fold1<R>(acc, va[u].z, vb[u].z);
+      acc = fold1<R>(acc, va[u].w, vb[u].w);
+    }
+  }
+  for (; c < d; c += 128) {
     if (c + 4 <= d) {
       float4 va = ld4(a + c), vb = ld4(b + c);
       acc = fold1<R>(acc, va.x, vb.x);

@@ -44,12 +44,40 @@ struct FinalizeParams {
 };
 
 // Block-wide radix select: returns the `keep`-th largest of the n distinct keys in s[0..n) (n >= keep >= 1).
-// 8 passes over 8-bit digits from the top; O(n) work instead of a full sort.  hist_s: 256 ints, sel_s: 2 ints.
+// 8-bit digits from the top, O(n) work instead of a full sort; the leading digits on which all keys agree are
+// skipped (candidate scores share sign, exponent and the first mantissa bits).  (Merging same-bin lanes with
+// __match_any_sync was tried and lost: the match costs more than the serialised shared atomics it saves.)
+// hist_s: 256 ints, sel_s: 2 ints.
 __device__ __forceinline__ uint64_t block_radix_kth(const uint64_t* s, int n, int keep, int* hist_s, int* sel_s) {
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
-  uint64_t prefix = 0ull;
+  // common prefix: OR and AND of all keys (two 64-bit words kept as 4 ints in hist_s[0..3])
+  if (tid < 4) hist_s[tid] = (tid & 1) ? -1 : 0;   // [0],[2]: OR halves   [1],[3]: AND halves
+  __syncthreads();
+  {
+    uint64_t o = 0ull, a = ~0ull;
+    for (int i = tid; i < n; i += nt) { const uint64_t k = s[i]; o |= k; a &= k; }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      o |= __shfl_xor_sync(kFull, o, off);
+      a &= __shfl_xor_sync(kFull, a, off);
+    }
+    if (lane == 0) {
+      atomicOr(&hist_s[0], int(uint32_t(o)));
+      atomicOr(&hist_s[2], int(uint32_t(o >> 32)));
+      atomicAnd(&hist_s[1], int(uint32_t(a)));
+      atomicAnd(&hist_s[3], int(uint32_t(a >> 32)));
+    }
+  }
+  __syncthreads();
+  const uint64_t all_or = (uint64_t(uint32_t(hist_s[2])) << 32) | uint32_t(hist_s[0]);
+  const uint64_t all_and = (uint64_t(uint32_t(hist_s[3])) << 32) | uint32_t(hist_s[1]);
+  __syncthreads();
+  const uint64_t diff = all_or ^ all_and;
+  if (diff == 0ull) return all_and;                                  // n == 1 (keys are distinct)
+  const int top = (63 - __clzll((long long)diff)) & ~7;              // shift of the first digit that differs
+  uint64_t prefix = top == 56 ? 0ull : (all_and & (~0ull << (top + 8)));
   int need = keep;
-  for (int shift = 56; shift >= 0; shift -= 8) {
+  for (int shift = top; shift >= 0; shift -= 8) {
     for (int i = tid; i < 256; i += nt) hist_s[i] = 0;
     __syncthreads();
     const uint64_t himask = shift == 56 ? 0ull : (~0ull << (shift + 8));
@@ -87,7 +115,7 @@ __device__ __forceinline__ uint64_t block_radix_kth(const uint64_t* s, int n, in
 
 // Gathers the keys of `nslots` lists (list s holds cnt_of(s) keys key_of(s, i)), drops zero keys and keys whose
 // score half is below thr_hi, and leaves the best `keep` in s[0..keep) sorted descending (s has sortn entries,
-// sortn >= keep + blockDim).  Returns min(#kept keys, keep).  Block-collective; off_s is [kFinMaxSlots + 1] ints.
+// sortn >= keep + 2048).  Returns min(#kept keys, keep).  Block-collective; off_s is [kFinMaxSlots + 1] ints.
 template <typename CntF, typename KeyF>
 __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int nslots, CntF cnt_of, KeyF key_of,
                                            uint32_t thr_hi, int* off_s, int* fill_s, unsigned long long* seen,
@@ -115,8 +143,11 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
   const int total = off_s[nslots];
   int fill = 0;   // uniform copy of *fill_s
   unsigned long long mine = 0;
-  for (int base = 0; base < total; base += nt) {
-    if (fill + nt > sortn) {   // make room: keep the best `keep` so far (radix select + compaction, O(fill))
+  // Gather rounds of nt*U entries: every thread issues its U loads back to back (the entries sit at scattered
+  // addresses: one outstanding load per thread and a barrier per round made this loop latency-bound).
+  const int U = max(1, min(8, 2048 / nt));
+  for (int base = 0; base < total; base += nt * U) {
+    if (fill + nt * U > sortn) {   // make room: keep the best `keep` so far (radix select + compaction, O(fill))
       const uint64_t kth = block_radix_kth(s, fill, keep, hist_sh, hist_sh + 256);
       if (tid == 0) *fill_s = 0;
       __syncthreads();
@@ -133,22 +164,31 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
       if (tid == 0) *fill_s = fill;
       __syncthreads();
     }
-    const int e = base + tid;
-    bool pass = false;
-    if (e < total) {
-      int lo = 0, hi = nslots;            // largest slot with off_s[slot] <= e
-      while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (off_s[mid] <= e) lo = mid; else hi = mid;
+    uint64_t keys[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      keys[u] = 0ull;
+      const int e = base + u * nt + tid;
+      if (u < U && e < total) {
+        int lo = 0, hi = nslots;            // largest slot with off_s[slot] <= e
+        while (hi - lo > 1) {
+          int mid = (lo + hi) >> 1;
+          if (off_s[mid] <= e) lo = mid; else hi = mid;
+        }
+        keys[u] = key_of(lo, e - off_s[lo]);
       }
-      const uint64_t key = key_of(lo, e - off_s[lo]);
-      pass = key != 0ull && uint32_t(key >> 32) >= thr_hi;
-      if (pass) {
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const uint64_t key = keys[u];
+      if (key != 0ull && uint32_t(key >> 32) >= thr_hi) {
         s[atomicAdd(fill_s, 1)] = key;
         ++mine;
       }
     }
-    fill += __syncthreads_count(pass);
+    __syncthreads();
+    fill = *fill_s;       // uniform: nobody appends between the two barriers
+    __syncthreads();
   }
   if (seen) {   // one global atomic per warp, not per thread
     unsigned long long w = mine;
