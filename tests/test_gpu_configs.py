@@ -187,3 +187,30 @@ def test_exact_mode_with_bf16_shadow(oracle, metric):
     assert np.array_equal(idx.reconstruct(77), x[77])
     with pytest.raises(b2r.B2RError):
         b2r.IndexFlatIP(64, storage="bf16", shadow=True)
+
+
+def test_random_shapes_against_the_oracle(oracle):
+    """40 seeded random (n, d, nq, k, metric, storage, engine) cases, small enough for the exhaustive oracle."""
+    rng = np.random.default_rng(2026)
+    for case in range(40):
+        n = int(rng.integers(1, 3000))
+        d = int(rng.integers(1, 300))
+        nq = int(rng.integers(1, 300))
+        k = int(rng.integers(1, 50))
+        metric = int(rng.integers(0, 2))
+        storage = ["f32", "bf16"][int(rng.integers(0, 2))]
+        engine = [b2r.ENGINE_AUTO, b2r.ENGINE_FMA, b2r.ENGINE_UMMA3][int(rng.integers(0, 3))]
+        if storage == "bf16" and engine == b2r.ENGINE_UMMA3:
+            engine = b2r.ENGINE_AUTO
+        x = rng.standard_normal((n, d)).astype(np.float32)
+        q = rng.standard_normal((nq, d)).astype(np.float32)
+        if case % 3 == 0 and n > 10:
+            x[n // 2:] = x[: n - n // 2]                 # duplicate rows: exact ties
+        idx = b2r.IndexFlat(d, metric, storage=storage, shadow=(storage == "f32" and case % 4 == 1))
+        idx.set_engine(engine)
+        idx.add(x)
+        D, I = idx.search(q, k)
+        xo, qo = (oracle.round_bf16(x), oracle.round_bf16(q)) if storage == "bf16" else (x, q)
+        D0, I0 = oracle.search_defined(xo, qo, k, metric)
+        assert np.array_equal(I, I0), (case, n, d, nq, k, metric, storage, engine)
+        assert np.array_equal(_bits(D), _bits(D0)), (case, n, d, nq, k, metric, storage, engine)
