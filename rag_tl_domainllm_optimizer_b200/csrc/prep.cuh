@@ -53,6 +53,7 @@ __global__ void __launch_bounds__(256) ingest_rows_kernel(const float* __restric
     }
     // write the stored row, accumulate its squared norm in the same DOT64 order
     double acc = 0.0;
+#pragma unroll 4
     for (int c = lane * 4; c < ld; c += 128) {
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (c + 4 <= d && vec_in) {
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(256) normalize_inplace_kernel(float* __restric
     float nrm = float(sqrt(ss));
     if (nrm == 0.f) continue;
     if (vec) {
+#pragma unroll 4
       for (int c = lane * 4; c < d; c += 128) {
         float4 v = ld4(row + c);
         v.x = v.x / nrm; v.y = v.y / nrm; v.z = v.z / nrm; v.w = v.w / nrm;
