@@ -389,11 +389,11 @@ static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, Final
   const int grid = int(std::max<int64_t>(1, std::min<int64_t>(ntiles, int64_t(idx->sm_count) * 2)));
   int cap = host_next_pow2(std::max(2 * kp, kp + 2 * kFmaTile));
   size_t smem = size_t(kFmaQB) * idx->ld * 4 + size_t(kFmaQB) * cap * 8;
-  if (smem > 227 * 1024) {   // large k: settle for the smallest buffer that still absorbs one tile between compactions
+  if (smem > 226 * 1024) {   // large k: settle for the smallest buffer that still absorbs one tile between compactions
     cap = host_next_pow2(kp + 2 * kFmaTile);
     smem = size_t(kFmaQB) * idx->ld * 4 + size_t(kFmaQB) * cap * 8;
   }
-  if (smem > 227 * 1024)
+  if (smem > 226 * 1024)
     return fail(B2R_ERR_LIMIT, "FMA engine needs %zu bytes of shared memory (d=%lld, k'=%d); limit is 232448", smem, (long long)idx->d, kp);
   RC_TRY(idx->cand.ensure(size_t(grid) * nq * kp * 8));
   FmaParams p{};
@@ -403,10 +403,19 @@ static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, Final
   p.thr = static_cast<uint32_t*>(idx->thr.p);
   p.cand = static_cast<uint64_t*>(idx->cand.p);
   p.nq = int(nq); p.kp = kp; p.cap = cap;
-  if (idx->storage == B2R_STORE_BF16)
-    CU_TRY(cudaFuncSetAttribute(score_fma_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-  else
-    CU_TRY(cudaFuncSetAttribute(score_fma_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  {   // opt in to the full 227 KiB once per device and instance (never lowered: other handles may be launching)
+    static std::mutex mu;
+    static bool done[64][2] = {};
+    std::lock_guard<std::mutex> lk(mu);
+    const int which = idx->storage == B2R_STORE_BF16 ? 1 : 0;
+    if (idx->device < 64 && !done[idx->device][which]) {
+      if (which)
+        CU_TRY(cudaFuncSetAttribute(score_fma_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+      else
+        CU_TRY(cudaFuncSetAttribute(score_fma_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+      done[idx->device][which] = true;
+    }
+  }
   for (int64_t q0 = 0; q0 < nq; q0 += kFmaQB) {
     p.q0 = int(q0);
     p.nqb = int(std::min<int64_t>(kFmaQB, nq - q0));
@@ -424,6 +433,22 @@ static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, Final
   fp.per = kp;
   fp.cnt = nullptr;
   fp.errfac = float((double(idx->d) + 8.0) * 6.1e-8);   // (d+8) * 2^-24 * 1.02
+  return B2R_OK;
+}
+
+// finalize_kernel's dynamic shared memory ((sortn + K'2) * 8 <= 48 KiB + its static arrays) needs the opt-in
+// attribute; it is set to a fixed 64 KiB once per device and kernel instance, never lowered.
+static int finalize_smem_once(int device, int which) {
+  static std::mutex mu;
+  static bool done[64][2] = {};
+  std::lock_guard<std::mutex> lk(mu);
+  if (device < 0 || device >= 64) return fail(B2R_ERR_ARG, "device %d out of range", device);
+  if (done[device][which]) return B2R_OK;
+  if (which)
+    CU_TRY(cudaFuncSetAttribute(finalize_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  else
+    CU_TRY(cudaFuncSetAttribute(finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  done[device][which] = true;
   return B2R_OK;
 }
 
@@ -518,10 +543,10 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   fp.stats = static_cast<unsigned long long*>(idx->stats.p);
   const size_t smem = size_t(fp.sortn + host_next_pow2(kp)) * 8;
   if (idx->storage == B2R_STORE_BF16) {
-    CU_TRY(cudaFuncSetAttribute(finalize_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    RC_TRY(finalize_smem_once(idx->device, 1));
     finalize_kernel<__nv_bfloat16><<<int(nq), fin_threads, smem, st>>>(fp);
   } else {
-    CU_TRY(cudaFuncSetAttribute(finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    RC_TRY(finalize_smem_once(idx->device, 0));
     finalize_kernel<float><<<int(nq), fin_threads, smem, st>>>(fp);
   }
   CU_TRY(cudaGetLastError());
