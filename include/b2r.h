@@ -147,6 +147,7 @@ int b2r_index_import_rows(b2r_index* idx, int64_t n, const void* rows, void* str
  * the tail is padded with I=-1 and D=-FLT_MAX (IP) / +FLT_MAX (L2).
  * `row_offset` is added to every returned id (global id of a row-sharded corpus).
  * If `normalize_queries` is non-zero a normalised copy of the queries is searched.
+ * Calls with more than 8192 queries are walked in batches of 8192 (bounded scratch).
  * Replaces: faiss `Index::search(n, x, k, distances, labels)` — the call made by
  * LangChain `FAISS.similarity_search_with_score_by_vector` and LlamaIndex
  * `FaissVectorStore.query`, whose output feeds

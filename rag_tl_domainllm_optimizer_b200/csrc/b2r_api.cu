@@ -138,6 +138,7 @@ struct b2r_index {
   float* maxnorm2 = nullptr;  // device scalar: largest stored squared norm
   int sm_count = 148;
   int engine = B2R_ENGINE_AUTO, pad = 6;
+  bool last_is_sum = false;            // idx->last holds the sum over the batches of one large call
   bool verify = true;                  // exact mode: re-run unproven tensor-core searches on the FMA engine
   unsigned long long* host_flag = nullptr;   // pinned, for that check
   // per-search workspace
@@ -552,13 +553,14 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   CU_TRY(cudaGetLastError());
   ++launches;
   idx->last = b2r_search_stats{};
+  idx->last_is_sum = false;
   idx->last.nq = nq; idx->last.k = k; idx->last.kprime = kp;
   idx->last.engine = engine_used; idx->last.launches = launches; idx->last.main_rows = main_rows;
   return B2R_OK;
 }
 
-static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries, int64_t row_offset,
-                      float* D, int64_t* I, uint64_t* packed, void* stream) {
+static int search_batch(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries, int64_t row_offset,
+                        float* D, int64_t* I, uint64_t* packed, void* stream) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
   if (nq < 0) return fail(B2R_ERR_ARG, "negative query count");
   if (k <= 0) return fail(B2R_ERR_ARG, "k must be positive (got %lld)", (long long)k);
@@ -626,6 +628,30 @@ static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int
   return B2R_OK;
 }
 
+// Large query sets go through in batches of 8192 queries so that the candidate scratch stays bounded
+// (the corpus is streamed once per 2048 queries either way).
+static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries, int64_t row_offset,
+                      float* D, int64_t* I, uint64_t* packed, void* stream) {
+  constexpr int64_t kBatch = 8192;
+  if (!idx || nq <= kBatch || !q || k <= 0 || k > 1024)
+    return search_batch(idx, nq, q, k, normalize_queries, row_offset, D, I, packed, stream);
+  b2r_search_stats total{};
+  for (int64_t q0 = 0; q0 < nq; q0 += kBatch) {
+    const int64_t m = std::min(kBatch, nq - q0);
+    RC_TRY(search_batch(idx, m, q + q0 * idx->d, k, normalize_queries, row_offset, D ? D + q0 * k : nullptr,
+                        I ? I + q0 * k : nullptr, packed ? packed + q0 * k : nullptr, stream));
+    b2r_search_stats st;
+    RC_TRY(b2r_index_last_stats(idx, &st));      // per-batch counters are summed (synchronises)
+    total.nq += st.nq; total.unverified += st.unverified; total.candidates += st.candidates;
+    total.launches += st.launches; total.fallback |= st.fallback;
+    total.k = st.k; total.kprime = st.kprime; total.engine = st.engine; total.main_rows = st.main_rows;
+  }
+  std::lock_guard<std::mutex> lk(idx->mu);
+  idx->last = total;
+  idx->last_is_sum = true;
+  return B2R_OK;
+}
+
 extern "C" int b2r_index_search(b2r_index* idx, int64_t nq, const float* q, int64_t k, float* D, int64_t* I, void* stream) {
   return search_any(idx, nq, q, k, 0, 0, D, I, nullptr, stream);
 }
@@ -666,8 +692,10 @@ extern "C" int b2r_index_last_stats(b2r_index* idx, b2r_search_stats* out) {
     CU_TRY(cudaDeviceSynchronize());
     CU_TRY(cudaMemcpy(h, idx->stats.p, sizeof h, cudaMemcpyDeviceToHost));
   }
-  idx->last.unverified = int64_t(h[0]);
-  idx->last.candidates = int64_t(h[1]);
+  if (!idx->last_is_sum) {   // a batched call already summed its per-batch counters
+    idx->last.unverified = int64_t(h[0]);
+    idx->last.candidates = int64_t(h[1]);
+  }
   *out = idx->last;
   return B2R_OK;
 }

@@ -214,3 +214,16 @@ def test_random_shapes_against_the_oracle(oracle):
         D0, I0 = oracle.search_defined(xo, qo, k, metric)
         assert np.array_equal(I, I0), (case, n, d, nq, k, metric, storage, engine)
         assert np.array_equal(_bits(D), _bits(D0)), (case, n, d, nq, k, metric, storage, engine)
+
+
+def test_more_queries_than_one_batch(oracle):
+    """20k queries in one call: the C ABI walks them in batches of 8192 with a bounded scratch."""
+    x, q = _data(oracle, 6000, 64, 20_000, 95)
+    for storage in ("f32", "bf16"):
+        idx = b2r.IndexFlatIP(64, storage=storage)
+        idx.add(x)
+        D, I = idx.search(q, 5)
+        xo, qo = (oracle.round_bf16(x), oracle.round_bf16(q)) if storage == "bf16" else (x, q)
+        _check(D, I, *oracle.search_ref(xo, qo, 5, 0))
+        st = idx.last_stats()
+        assert st["nq"] == 20_000 and st["unverified"] == 0
