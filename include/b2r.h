@@ -167,6 +167,20 @@ int b2r_index_search_packed(b2r_index* idx, int64_t nq, const float* q, int64_t 
                             int normalize_queries, int64_t row_offset,
                             uint64_t* packed, void* stream);
 
+/* b2r_index_search_packed without the host-side proof check: `packed` has nq*k + 1 entries and the
+ * last one receives the number of unproven queries of this shard (exact mode), so that the flag
+ * travels inside the all-gather payload and no host sync precedes the collective.  The caller reads
+ * the gathered flags once everything is enqueued and, if any is non-zero, repeats the search on every
+ * rank with b2r_index_set_engine(B2R_ENGINE_UMMA3).  At most 8192 queries per call. */
+int b2r_index_search_packed_async(b2r_index* idx, int64_t nq, const float* q, int64_t k,
+                                  int normalize_queries, int64_t row_offset,
+                                  uint64_t* packed, void* stream);
+
+/* b2r_merge_packed for lists that are g_stride (>= nq*k) elements apart, e.g. the gathered
+ * payloads of b2r_index_search_packed_async (g_stride = nq*k + 1). */
+int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed,
+                             int64_t g_stride, float* D, int64_t* I, int device, void* stream);
+
 /* Merge G gathered packed lists ([G,nq,k], device) into the final D/I ([nq,k]).
  * The comparator is the one of b2r_index_search, so a row-sharded search equals the
  * unsharded one.  No counterpart in faiss CPU; it is what `IndexShards` does on host. */

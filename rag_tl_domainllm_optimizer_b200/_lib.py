@@ -27,7 +27,8 @@ EXPORTS = [
     "b2r_index_reserve", "b2r_index_reset", "b2r_index_ntotal", "b2r_index_reconstruct", "b2r_index_search",
     "b2r_index_search_ex", "b2r_index_search_packed", "b2r_merge_packed", "b2r_index_set_engine",
     "b2r_index_set_pad", "b2r_index_last_stats", "b2r_index_last_score_ms", "b2r_index_score_time", "b2r_normalize_l2", "b2r_cosine_rows",
-    "b2r_cosine_rows_noalloc", "b2r_index_export_rows", "b2r_index_import_rows", "b2r_index_set_shadow", "b2r_index_set_verify",
+    "b2r_cosine_rows_noalloc", "b2r_index_export_rows", "b2r_index_import_rows", "b2r_index_set_shadow", "b2r_index_set_verify", "b2r_index_search_packed_async",
+    "b2r_merge_packed_strided",
 ]
 
 
@@ -83,6 +84,8 @@ def lib() -> ctypes.CDLL:
     L.b2r_index_search_ex.argtypes = [vp, i64, vp, i64, i32, i64, vp, vp, vp]
     L.b2r_index_search_packed.argtypes = [vp, i64, vp, i64, i32, i64, vp, vp]
     L.b2r_merge_packed.argtypes = [i32, i64, i64, i64, vp, vp, vp, i32, vp]
+    L.b2r_merge_packed_strided.argtypes = [i32, i64, i64, i64, vp, i64, vp, vp, i32, vp]
+    L.b2r_index_search_packed_async.argtypes = [vp, i64, vp, i64, i32, i64, vp, vp]
     L.b2r_index_set_engine.argtypes = [vp, i32]
     L.b2r_index_set_pad.argtypes = [vp, i32]
     L.b2r_index_set_shadow.argtypes = [vp, i32]

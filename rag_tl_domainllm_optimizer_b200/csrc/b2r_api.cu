@@ -560,7 +560,7 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
 }
 
 static int search_batch(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries, int64_t row_offset,
-                        float* D, int64_t* I, uint64_t* packed, void* stream) {
+                        float* D, int64_t* I, uint64_t* packed, void* stream, uint64_t* flag_out = nullptr) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
   if (nq < 0) return fail(B2R_ERR_ARG, "negative query count");
   if (k <= 0) return fail(B2R_ERR_ARG, "k must be positive (got %lld)", (long long)k);
@@ -601,8 +601,10 @@ static int search_batch(b2r_index* idx, int64_t nq, const float* q, int64_t k, i
     }
     return B2R_OK;
   };
+  if (flag_out)   // deferred proof: the caller reads the unverified count later (it rides in its all-gather payload)
+    CU_TRY(cudaMemcpyAsync(flag_out, idx->stats.p, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
   const bool check_proof = (idx->last.engine == B2R_ENGINE_UMMA || idx->last.engine == B2R_ENGINE_SHADOW) &&
-                           idx->storage == B2R_STORE_F32 && idx->verify;
+                           idx->storage == B2R_STORE_F32 && idx->verify && !flag_out;
   if (check_proof) {
     // exact mode on the tensor cores is only as good as its proof: read the counter of unproven queries and, if
     // any, search again with the 3xTF32 split (error bound ~30x tighter; FMA engine where tcgen05 cannot take the
@@ -665,8 +667,25 @@ extern "C" int b2r_index_search_packed(b2r_index* idx, int64_t nq, const float* 
   return search_any(idx, nq, q, k, normalize_queries, row_offset, nullptr, nullptr, packed, stream);
 }
 
+extern "C" int b2r_index_search_packed_async(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries,
+                                             int64_t row_offset, uint64_t* packed, void* stream) {
+  if (!packed) return fail(B2R_ERR_ARG, "packed is null");
+  if (nq > 8192) return fail(B2R_ERR_LIMIT, "b2r_index_search_packed_async takes at most 8192 queries per call");
+  if (nq <= 0 || k <= 0) return fail(B2R_ERR_ARG, "bad shape nq=%lld k=%lld", (long long)nq, (long long)k);
+  return search_batch(idx, nq, q, k, normalize_queries, row_offset, nullptr, nullptr, packed, stream, packed + nq * k);
+}
+
+extern "C" int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed,
+                                        int64_t g_stride, float* D, int64_t* I, int device, void* stream);
+
 extern "C" int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed, float* D,
                                 int64_t* I, int device, void* stream) {
+  return b2r_merge_packed_strided(metric, G, nq, k, packed, nq * k, D, I, device, stream);
+}
+
+extern "C" int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed,
+                                        int64_t g_stride, float* D, int64_t* I, int device, void* stream) {
+  if (g_stride < nq * k) return fail(B2R_ERR_ARG, "g_stride %lld is smaller than nq*k", (long long)g_stride);
   if (metric != B2R_METRIC_IP && metric != B2R_METRIC_L2) return fail(B2R_ERR_ARG, "unknown metric %d", metric);
   if (G <= 0 || nq < 0 || k <= 0) return fail(B2R_ERR_ARG, "bad shape G=%lld nq=%lld k=%lld", (long long)G, (long long)nq, (long long)k);
   if (k > 1024) return fail(B2R_ERR_LIMIT, "k=%lld exceeds the supported maximum of 1024", (long long)k);
@@ -678,7 +697,7 @@ extern "C" int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k, co
   if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int sortn = std::max(4096, host_next_pow2(int(k) + 2048));   // gather rounds append up to 2048 keys
-  merge_packed_kernel<<<int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st>>>(packed, int(G), int(nq), int(k), sortn, metric, D, I);
+  merge_packed_kernel<<<int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st>>>(packed, int(G), int(nq), int(k), g_stride, sortn, metric, D, I);
   CU_TRY(cudaGetLastError());
   return B2R_OK;
 }

@@ -302,6 +302,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
 
 // Merge of G all-gathered packed lists [G][nq][k] -> D/I [nq][k].
 __global__ void __launch_bounds__(256) merge_packed_kernel(const uint64_t* __restrict__ packed, int G, int nq, int k,
+                                                           int64_t g_stride /* elements between ranks' lists */,
                                                            int sortn, int metric, float* __restrict__ D,
                                                            int64_t* __restrict__ I) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -310,7 +311,7 @@ __global__ void __launch_bounds__(256) merge_packed_kernel(const uint64_t* __res
   __shared__ int off_s[kFinMaxSlots + 1];
   const int q = blockIdx.x;
   auto cnt_of = [&](int) -> int { return k; };
-  auto key_of = [&](int g, int i) -> uint64_t { return packed[(int64_t(g) * nq + q) * k + i]; };
+  auto key_of = [&](int g, int i) -> uint64_t { return packed[int64_t(g) * g_stride + int64_t(q) * k + i]; };
   const int got = gather_topk(s, sortn, k, G, cnt_of, key_of, 0u, off_s, &fill_s, nullptr, s + sortn);
   for (int j = threadIdx.x; j < k; j += blockDim.x) {
     const bool have = j < got;

@@ -80,6 +80,7 @@ class IndexFlat:
         self.device = int(device)
         self.normalize = bool(normalize)   # cosine index: rows and queries are L2-normalised on the way in
         self.is_trained = True
+        self.engine = ENGINE_AUTO
         self._h = ctypes.c_void_p()
         L = _lib.lib()
         check(L.b2r_index_create(ctypes.byref(self._h), self.d, self.metric_type,
@@ -156,9 +157,23 @@ class IndexFlat:
                                                  packed.data_ptr(), stream))
         return packed
 
+    def search_packed_async(self, x, k: int, row_offset: int = 0):
+        """Like ``search_packed`` but without the host-side proof check: returns a CUDA int64 tensor of
+        ``n*k + 1`` entries whose last one is this shard's count of unproven queries (exact mode)."""
+        torch = _torch()
+        kind, obj, ptr, n, stream, dev = _as_f32_2d(x, self.d, "x")
+        device = torch.device("cuda", self.device)
+        if kind != "cuda":
+            stream = torch.cuda.current_stream(device).cuda_stream
+        buf = torch.empty((n * int(k) + 1,), dtype=torch.int64, device=device)
+        check(_lib.lib().b2r_index_search_packed_async(self._h, n, ptr, int(k), int(self.normalize), int(row_offset),
+                                                       buf.data_ptr(), stream))
+        return buf
+
     # -- tuning / introspection ------------------------------------------------------------
     def set_engine(self, engine: int) -> None:
         check(_lib.lib().b2r_index_set_engine(self._h, int(engine)))
+        self.engine = int(engine)
 
     def set_verify(self, on: bool) -> None:
         """Exact mode: proof read-back + fallback after each search (default on; off keeps searches asynchronous)."""
@@ -206,6 +221,20 @@ def merge_packed(packed, metric: int = METRIC_INNER_PRODUCT):
     I = torch.empty((n, k), dtype=torch.int64, device=packed.device)
     check(_lib.lib().b2r_merge_packed(int(metric), G, n, k, packed.data_ptr(), D.data_ptr(), I.data_ptr(),
                                       packed.device.index, torch.cuda.current_stream(packed.device).cuda_stream))
+    return D, I
+
+
+def merge_packed_strided(gathered, n: int, k: int, metric: int = METRIC_INNER_PRODUCT):
+    """[G, n*k + 1] payloads of ``search_packed_async`` (CUDA int64) -> (D [n,k], I [n,k])."""
+    torch = _torch()
+    if gathered.dim() != 2 or not gathered.is_cuda or gathered.dtype != torch.int64 or gathered.shape[1] < n * k:
+        raise ShapeError("gathered must be a CUDA int64 tensor of shape [G, >= n*k]")
+    gathered = gathered.contiguous()
+    D = torch.empty((n, k), dtype=torch.float32, device=gathered.device)
+    I = torch.empty((n, k), dtype=torch.int64, device=gathered.device)
+    check(_lib.lib().b2r_merge_packed_strided(int(metric), gathered.shape[0], n, k, gathered.data_ptr(),
+                                              gathered.shape[1], D.data_ptr(), I.data_ptr(), gathered.device.index,
+                                              torch.cuda.current_stream(gathered.device).cuda_stream))
     return D, I
 
 

@@ -12,7 +12,7 @@ from typing import Tuple
 import numpy as np
 
 from ._lib import METRIC_INNER_PRODUCT
-from .index import IndexFlat, merge_packed
+from .index import IndexFlat, merge_packed, merge_packed_strided
 
 
 def shard_bounds(n: int, world: int, rank: int) -> Tuple[int, int]:
@@ -49,6 +49,33 @@ class ShardedIndexFlat:
         import torch
         if self.world == 1 and self.row_offset == 0 and hasattr(self.local, "search"):
             return self.local.search(x, k)                                # one shard: nothing to gather or merge
+        if not hasattr(self.local, "search_packed_async") or len(x) > 8192:
+            return self._search_synchronous(x, k)
+        # Everything is enqueued before the host looks at anything: shard-local search (its count of unproven
+        # queries rides as the last word of the payload), the single all-gather, the merge.
+        n, k = len(x), int(k)
+        buf = self.local.search_packed_async(x, k, self.row_offset)      # [n*k + 1] on this GPU
+        gathered = torch.empty((self.world, n * k + 1), dtype=buf.dtype, device=buf.device)
+        self._dist.all_gather_into_tensor(gathered, buf.view(1, -1), group=self.group)   # the single collective
+        D, I = merge_packed_strided(gathered, n, k, self.metric_type)
+        if self.local.storage == "f32" and int(gathered[:, n * k].max().item()) != 0:
+            # some shard could not prove its top-k (exact mode): every rank saw the same flags, so every rank
+            # repeats the search with the 3xTF32 variant
+            from ._lib import ENGINE_FMA, ENGINE_UMMA3, B2RError
+            previous = getattr(self.local, "engine", 0)
+            try:
+                self.local.set_engine(ENGINE_UMMA3)
+                try:
+                    D, I = self._search_synchronous(x, k)
+                except B2RError:                      # a shape tcgen05 does not take: the FMA engine does
+                    self.local.set_engine(ENGINE_FMA)
+                    D, I = self._search_synchronous(x, k)
+            finally:
+                self.local.set_engine(previous)
+        return D, I
+
+    def _search_synchronous(self, x, k: int):
+        import torch
         packed = self.local.search_packed(x, k, self.row_offset)          # [nq,k] on this GPU
         if self.world == 1:
             return self._merge(packed.unsqueeze(0), self.metric_type)

@@ -227,3 +227,26 @@ def test_more_queries_than_one_batch(oracle):
         _check(D, I, *oracle.search_ref(xo, qo, 5, 0))
         st = idx.last_stats()
         assert st["nq"] == 20_000 and st["unverified"] == 0
+
+
+def test_async_packed_search_carries_the_proof_flag(oracle):
+    """The sharded path's payload: n*k packed hits + 1 word = the shard's count of unproven queries."""
+    import torch
+    x, q = _data(oracle, 40_001, 128, 33, 97)
+    D0, I0 = oracle.search_ref(x, q, 10, 0)
+    for G in (2, 3):
+        bufs = []
+        for r in range(G):
+            lo, hi = b2r.shard_bounds(len(x), G, r)
+            sh = b2r.IndexFlatIP(128)
+            sh.add(x[lo:hi])
+            bufs.append(sh.search_packed_async(q, 10, lo))
+        gathered = torch.stack(bufs)
+        assert gathered.shape == (G, 33 * 10 + 1) and int(gathered[:, -1].max().item()) == 0
+        D, I = b2r.merge_packed_strided(gathered, 33, 10, 0)
+        _check(D.cpu().numpy(), I.cpu().numpy(), D0, I0)
+    x[300:340] = x[5]                                   # tie cluster: shard 0 cannot prove query 0
+    q[0] = x[5]
+    sh = b2r.IndexFlatIP(128)
+    sh.add(x[:20_000])
+    assert int(sh.search_packed_async(q, 10, 0)[-1].item()) >= 1
