@@ -62,8 +62,8 @@ enum {
   B2R_ENGINE_FMA = 1,   /* CUDA-core fp32 FMA streaming kernel                        */
   B2R_ENGINE_UMMA = 2,  /* TMA + tcgen05.mma + TMEM kernel: kind::f16 on bf16 rows,   */
                         /* one kind::tf32 pass on fp32 rows                           */
-  B2R_ENGINE_UMMA3 = 3, /* the same kernel with the 3xTF32 split (fp32 rows): the     */
-                        /* fallback of exact mode when the 1xTF32 proof fails         */
+  B2R_ENGINE_UMMA3 = 3, /* the same kernel with the 3xTF32 split (fp32 rows); also    */
+                        /* what exact mode's second (range) pass runs                 */
   B2R_ENGINE_SHADOW = 4 /* reported only: kind::f16 on the bf16 shadow of fp32 rows   */
                         /* (b2r_index_set_shadow), exact re-scoring on the fp32 rows  */
 };
@@ -73,18 +73,23 @@ typedef struct b2r_search_stats {
   int64_t nq;             /* queries in the call                                        */
   int64_t k;              /* requested k                                                */
   int64_t kprime;         /* candidates kept per query before exact re-scoring          */
-  int64_t unverified;     /* queries whose top-k could not be PROVEN complete by the    */
-                          /* error bound of the scoring pass; 0 means  */
-                          /* the returned ids are provably the exact top-k              */
-  int64_t candidates;     /* candidate entries that reached the merge kernel            */
-  int32_t engine;         /* B2R_ENGINE_FMA / _UMMA / _UMMA3 actually used              */
+  int64_t unverified;     /* queries whose top-k is NOT proven complete when the call   */
+                          /* is over.  Always 0 by default: a query the first pass      */
+                          /* cannot prove is re-searched on the device */
+                          /* (range pass, then the exhaustive scan, which cannot fail). */
+                          /* Non-zero only after b2r_index_set_verify(idx, 0).          */
+  int64_t candidates;     /* candidate entries that reached the merge kernels           */
+  int32_t engine;         /* B2R_ENGINE_FMA / _UMMA / _UMMA3 / _SHADOW of the first pass */
   int32_t launches;       /* kernels launched by the call                               */
-  int32_t fallback;       /* 1 if an exact-mode tensor-core search could not be proven  */
-                          /* and the call was repeated with 3xTF32 (or the FMA engine)   */
+  int32_t fallback;       /* 1 if any query needed the second pass                      */
   int32_t reserved;
   int64_t main_rows;      /* rows covered by the launch(es) that b2r_index_score_time times: */
                           /* the main tcgen05 launch (all rows but the seed rows), or all    */
                           /* rows for the FMA engine                                         */
+  int64_t fallback_queries;   /* queries the first pass could not prove: only these are     */
+                              /* searched again (range pass: every row above a fixed bound)  */
+  int64_t exhaustive_queries; /* of those, queries that went on to the exhaustive DOT64 scan */
+                              /* (their candidate set did not fit: thousands of tied rows)   */
 } b2r_search_stats;
 
 /* Library / device ------------------------------------------------------------------ */
@@ -167,17 +172,8 @@ int b2r_index_search_packed(b2r_index* idx, int64_t nq, const float* q, int64_t 
                             int normalize_queries, int64_t row_offset,
                             uint64_t* packed, void* stream);
 
-/* b2r_index_search_packed without the host-side proof check: `packed` has nq*k + 1 entries and the
- * last one receives the number of unproven queries of this shard (exact mode), so that the flag
- * travels inside the all-gather payload and no host sync precedes the collective.  The caller reads
- * the gathered flags once everything is enqueued and, if any is non-zero, repeats the search on every
- * rank with b2r_index_set_engine(B2R_ENGINE_UMMA3).  At most 8192 queries per call. */
-int b2r_index_search_packed_async(b2r_index* idx, int64_t nq, const float* q, int64_t k,
-                                  int normalize_queries, int64_t row_offset,
-                                  uint64_t* packed, void* stream);
-
-/* b2r_merge_packed for lists that are g_stride (>= nq*k) elements apart, e.g. the gathered
- * payloads of b2r_index_search_packed_async (g_stride = nq*k + 1). */
+/* b2r_merge_packed for lists that are g_stride (>= nq*k) elements apart (payloads that carry
+ * extra words behind the nq*k hits).  At most 1024 lists. */
 int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed,
                              int64_t g_stride, float* D, int64_t* I, int device, void* stream);
 
@@ -186,6 +182,25 @@ int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64_t k, const
  * unsharded one.  No counterpart in faiss CPU; it is what `IndexShards` does on host. */
 int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k,
                      const uint64_t* packed, float* D, int64_t* I, int device, void* stream);
+
+/* Row-sharded search: one process (or thread) and one handle per GPU, rank r holding the
+ * rows [row_offset, row_offset + ntotal) of the global corpus; every rank calls
+ * b2r_index_search_sharded with the SAME queries and k (collective semantics).  Each call enqueues, on
+ * `stream`: the shard-local search (packed top-k with global ids), ONE ncclAllGather of the
+ * nq*k*8-byte payloads into a buffer the handle owns and keeps, and the merge kernel — the result
+ * equals the unsharded search on every rank, ties included.  No host synchronisation for device
+ * pointers.  No faiss-CPU counterpart (IndexShards does the same merge on the host).
+ *
+ * b2r_index_set_comm adopts a communicator the caller created (an ncclComm_t, passed as void*; it must
+ * come from the NCCL library this process has loaded, which is the one b2r binds with dlopen); the
+ * handle does not destroy it.  b2r_index_comm_init creates one from a 128-byte ncclUniqueId that
+ * rank 0 obtained with b2r_nccl_unique_id and sent to the other ranks by any means; the handle owns
+ * and destroys it.  world == 1 needs no communicator (the call degenerates to a local search). */
+int b2r_nccl_unique_id(void* out128);
+int b2r_index_set_comm(b2r_index* idx, void* nccl_comm, int rank, int world, int64_t row_offset);
+int b2r_index_comm_init(b2r_index* idx, const void* unique_id128, int rank, int world, int64_t row_offset);
+int b2r_index_search_sharded(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries,
+                             float* D, int64_t* I, void* stream);
 
 /* Tuning / introspection ------------------------------------------------------------ */
 
@@ -197,16 +212,18 @@ int b2r_index_set_engine(b2r_index* idx, int engine);
  * those of exact mode (fp32 rows are re-scored, the proof and its fallback apply).  No faiss counterpart. */
 int b2r_index_set_shadow(b2r_index* idx, int on);
 
-/* Exact mode reads its proof counter after every tensor-core search and repeats unproven searches
- * with the 3xTF32 variant (default on; costs device-pointer callers one stream sync per search).
- * Turn it off to keep device-pointer searches fully asynchronous (e.g. under stream capture): the
- * counter is still kept (b2r_index_last_stats: `unverified`), the fallback becomes the caller's call. */
+/* By default every search ends with three launches that re-search, on the device and without any
+ * host round trip, exactly the queries whose top-k the first pass could not prove (range pass,
+ * its merge, exhaustive scan); they return at once when there is none.  on = 0 drops them: unproven
+ * queries are then only counted (b2r_index_last_stats: `unverified`) and handling them is the
+ * caller's call.  No faiss counterpart (faiss-CPU scores every row in fp32 and has nothing to prove). */
 int b2r_index_set_verify(b2r_index* idx, int on);
 
 /* Extra candidates kept per query before the exact re-scoring (default 6). */
 int b2r_index_set_pad(b2r_index* idx, int pad);
 
-/* Counters of the last search (synchronises the search's stream). */
+/* Counters of the last search.  Waits for that search's kernels only (an event recorded behind them),
+ * not for the device. */
 int b2r_index_last_stats(b2r_index* idx, b2r_search_stats* out);
 
 /* Milliseconds spent in the scoring kernel(s) alone during the last search, measured

@@ -27,8 +27,8 @@ EXPORTS = [
     "b2r_index_reserve", "b2r_index_reset", "b2r_index_ntotal", "b2r_index_reconstruct", "b2r_index_search",
     "b2r_index_search_ex", "b2r_index_search_packed", "b2r_merge_packed", "b2r_index_set_engine",
     "b2r_index_set_pad", "b2r_index_last_stats", "b2r_index_last_score_ms", "b2r_index_score_time", "b2r_normalize_l2", "b2r_cosine_rows",
-    "b2r_cosine_rows_noalloc", "b2r_index_export_rows", "b2r_index_import_rows", "b2r_index_set_shadow", "b2r_index_set_verify", "b2r_index_search_packed_async",
-    "b2r_merge_packed_strided",
+    "b2r_cosine_rows_noalloc", "b2r_index_export_rows", "b2r_index_import_rows", "b2r_index_set_shadow", "b2r_index_set_verify",
+    "b2r_merge_packed_strided", "b2r_nccl_unique_id", "b2r_index_set_comm", "b2r_index_comm_init", "b2r_index_search_sharded",
 ]
 
 
@@ -36,7 +36,8 @@ class SearchStats(ctypes.Structure):
     _fields_ = [("nq", ctypes.c_int64), ("k", ctypes.c_int64), ("kprime", ctypes.c_int64),
                 ("unverified", ctypes.c_int64), ("candidates", ctypes.c_int64), ("engine", ctypes.c_int32),
                 ("launches", ctypes.c_int32), ("fallback", ctypes.c_int32), ("reserved", ctypes.c_int32),
-                ("main_rows", ctypes.c_int64)]
+                ("main_rows", ctypes.c_int64), ("fallback_queries", ctypes.c_int64),
+                ("exhaustive_queries", ctypes.c_int64)]
 
 
 class B2RError(RuntimeError):
@@ -85,7 +86,10 @@ def lib() -> ctypes.CDLL:
     L.b2r_index_search_packed.argtypes = [vp, i64, vp, i64, i32, i64, vp, vp]
     L.b2r_merge_packed.argtypes = [i32, i64, i64, i64, vp, vp, vp, i32, vp]
     L.b2r_merge_packed_strided.argtypes = [i32, i64, i64, i64, vp, i64, vp, vp, i32, vp]
-    L.b2r_index_search_packed_async.argtypes = [vp, i64, vp, i64, i32, i64, vp, vp]
+    L.b2r_nccl_unique_id.argtypes = [vp]
+    L.b2r_index_set_comm.argtypes = [vp, vp, i32, i32, i64]
+    L.b2r_index_comm_init.argtypes = [vp, vp, i32, i32, i64]
+    L.b2r_index_search_sharded.argtypes = [vp, i64, vp, i64, i32, vp, vp, vp]
     L.b2r_index_set_engine.argtypes = [vp, i32]
     L.b2r_index_set_pad.argtypes = [vp, i32]
     L.b2r_index_set_shadow.argtypes = [vp, i32]

@@ -2,6 +2,7 @@
 // fallback: every compute entry point needs a CUDA device and fails loudly without one.
 #include <cuda_runtime.h>
 #include <cuda.h>
+#include <dlfcn.h>
 #include <float.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -16,6 +17,7 @@
 #include "common.cuh"
 #include "finalize.cuh"
 #include "prep.cuh"
+#include "score_exact.cuh"
 #include "score_fma.cuh"
 #include "score_umma.cuh"
 
@@ -64,12 +66,13 @@ extern "C" int b2r_device_count(void) {
 // --------------------------------------------------------------------------------------
 // small helpers
 // --------------------------------------------------------------------------------------
-static bool is_device_ptr(const void* p) {
+static bool is_device_ptr(const void* p, int* owner = nullptr) {
   cudaPointerAttributes a;
   if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
     cudaGetLastError();
     return false;
   }
+  if (owner) *owner = a.device;
   return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
@@ -126,6 +129,8 @@ struct DeviceGuard {
 // --------------------------------------------------------------------------------------
 // the handle
 // --------------------------------------------------------------------------------------
+struct NcclApi;   // dlopen'ed entry points of the NCCL library (sharded search), below
+
 struct b2r_index {
   int64_t d = 0;
   int metric = 0, storage = 0, device = 0;
@@ -138,17 +143,28 @@ struct b2r_index {
   float* maxnorm2 = nullptr;  // device scalar: largest stored squared norm
   int sm_count = 148;
   int engine = B2R_ENGINE_AUTO, pad = 6;
-  bool last_is_sum = false;            // idx->last holds the sum over the batches of one large call
-  bool verify = true;                  // exact mode: re-run unproven tensor-core searches on the FMA engine
-  unsigned long long* host_flag = nullptr;   // pinned, for that check
+  bool verify = true;                  // unproven queries go on to the range pass and the exhaustive scan (device side)
   // per-search workspace
   DevBuf qf, qh, qlo, qn2, thr, cand, cnt, stats, stage_q, stage_d, stage_i, stage_x, misc;
+  DevBuf fb;                           // hand-over lists of unproven queries: 16 counters, then 4 arrays of nq words
+  DevBuf qc_f, qc_lo, qc_h;            // their prepared rows, compacted, as the range pass reads them
+  DevBuf exl;                          // per-CTA top-k lists of the exhaustive scan
+  DevBuf shard_local, shard_all;       // sharded search: this rank's packed top-k, and every rank's
   static constexpr int kEvPool = 256;           // scoring-kernel timers: one event pair per recent search
   cudaEvent_t ev0[kEvPool] = {}, ev1[kEvPool] = {};
+  cudaEvent_t ev_done = nullptr;                // recorded after the last kernel of the most recent search
+  cudaStream_t side = nullptr;                  // non-blocking stream for the counters' read-back
   int64_t nrec = 0;                             // searches timed since the last timer reset
-  bool have_times = false;
+  bool have_times = false, searched = false;
+  int exact_occ[2] = {0, 0};                    // resident CTAs per SM of score_exact_kernel (per storage), 0 = unknown
+  size_t exact_occ_smem[2] = {0, 0};
   b2r_search_stats last{};
   UmmaState umma;         // tensor maps and scratch of the tcgen05 engine
+  // row-sharded search (b2r_index_set_comm / b2r_index_comm_init)
+  void* comm = nullptr;
+  bool comm_owned = false;
+  int rank = 0, world = 1;
+  int64_t row_offset = 0;
   std::mutex mu;
   size_t elem_bytes() const { return storage == B2R_STORE_BF16 ? 2 : 4; }
 };
@@ -177,36 +193,44 @@ extern "C" int b2r_index_create(b2r_index** out, int64_t d, int metric, int stor
   idx->sm_count = prop.multiProcessorCount;
   cudaError_t e = cudaMalloc(&idx->maxnorm2, sizeof(float));
   if (e == cudaSuccess) e = cudaMemset(idx->maxnorm2, 0, sizeof(float));
-  if (e == cudaSuccess) e = cudaMallocHost(&idx->host_flag, sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&idx->ev_done, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&idx->side, cudaStreamNonBlocking);
   for (int i = 0; i < b2r_index::kEvPool && e == cudaSuccess; ++i) {
     e = cudaEventCreate(&idx->ev0[i]);
     if (e == cudaSuccess) e = cudaEventCreate(&idx->ev1[i]);
   }
   if (e != cudaSuccess) {
-    delete idx;
+    cudaGetLastError();
+    b2r_index_free(idx);
     return fail(B2R_ERR_CUDA, "handle set-up failed: %s", cudaGetErrorString(e));
   }
   *out = idx;
   return B2R_OK;
 }
 
+static void comm_release(b2r_index* idx);
+
 extern "C" void b2r_index_free(b2r_index* idx) {
   if (!idx) return;
   DeviceGuard g(idx->device);
   cudaDeviceSynchronize();
+  comm_release(idx);
   if (idx->X) cudaFree(idx->X);
   if (idx->Xs) cudaFree(idx->Xs);
   if (idx->norm2) cudaFree(idx->norm2);
   if (idx->maxnorm2) cudaFree(idx->maxnorm2);
-  if (idx->host_flag) cudaFreeHost(idx->host_flag);
   DevBuf* bufs[] = {&idx->qf, &idx->qh, &idx->qlo, &idx->qn2, &idx->thr, &idx->cand, &idx->cnt, &idx->stats,
-                    &idx->stage_q, &idx->stage_d, &idx->stage_i, &idx->stage_x, &idx->misc};
+                    &idx->stage_q, &idx->stage_d, &idx->stage_i, &idx->stage_x, &idx->misc, &idx->fb, &idx->qc_f,
+                    &idx->qc_lo, &idx->qc_h, &idx->exl, &idx->shard_local, &idx->shard_all};
   for (DevBuf* b : bufs) b->release();
   idx->umma.release();
   for (int i = 0; i < b2r_index::kEvPool; ++i) {
     if (idx->ev0[i]) cudaEventDestroy(idx->ev0[i]);
     if (idx->ev1[i]) cudaEventDestroy(idx->ev1[i]);
   }
+  if (idx->ev_done) cudaEventDestroy(idx->ev_done);
+  if (idx->side) cudaStreamDestroy(idx->side);
+  cudaGetLastError();
   delete idx;
 }
 
@@ -216,6 +240,14 @@ static int grow(b2r_index* idx, int64_t rows, cudaStream_t st) {
   if (idx->cap_rows > 0) want = std::max<int64_t>(rows, idx->cap_rows + idx->cap_rows / 2);
   const size_t rowb = size_t(idx->ld) * idx->elem_bytes();
   void* nx = nullptr;
+  float* nn = nullptr;
+  void* ns = nullptr;
+  auto release_new = [&]() {
+    if (nx) cudaFree(nx);
+    if (nn) cudaFree(nn);
+    if (ns) cudaFree(ns);
+    cudaGetLastError();
+  };
   cudaError_t e = cudaMalloc(&nx, size_t(want) * rowb);
   if (e != cudaSuccess && want > rows) {
     cudaGetLastError();
@@ -226,30 +258,25 @@ static int grow(b2r_index* idx, int64_t rows, cudaStream_t st) {
     cudaGetLastError();
     return fail(B2R_ERR_OOM, "cannot allocate %zu bytes for %lld rows", size_t(want) * rowb, (long long)want);
   }
-  float* nn = nullptr;
-  if (idx->metric == B2R_METRIC_L2) {
-    e = cudaMalloc(&nn, size_t(want) * sizeof(float));
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      cudaFree(nx);
-      return fail(B2R_ERR_OOM, "cannot allocate row norms for %lld rows", (long long)want);
-    }
+  if (idx->metric == B2R_METRIC_L2 && cudaMalloc(&nn, size_t(want) * sizeof(float)) != cudaSuccess) {
+    release_new();
+    return fail(B2R_ERR_OOM, "cannot allocate row norms for %lld rows", (long long)want);
   }
-  void* ns = nullptr;
-  if (idx->shadow) {
-    e = cudaMalloc(&ns, size_t(want) * idx->ld * 2);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      cudaFree(nx);
-      if (nn) cudaFree(nn);
-      return fail(B2R_ERR_OOM, "cannot allocate the bf16 shadow for %lld rows", (long long)want);
-    }
-    if (idx->ntotal > 0) CU_TRY(cudaMemcpyAsync(ns, idx->Xs, size_t(idx->ntotal) * idx->ld * 2, cudaMemcpyDeviceToDevice, st));
+  if (idx->shadow && cudaMalloc(&ns, size_t(want) * idx->ld * 2) != cudaSuccess) {
+    release_new();
+    return fail(B2R_ERR_OOM, "cannot allocate the bf16 shadow for %lld rows", (long long)want);
   }
   if (idx->ntotal > 0) {
-    CU_TRY(cudaMemcpyAsync(nx, idx->X, size_t(idx->ntotal) * rowb, cudaMemcpyDeviceToDevice, st));
-    if (nn) CU_TRY(cudaMemcpyAsync(nn, idx->norm2, size_t(idx->ntotal) * sizeof(float), cudaMemcpyDeviceToDevice, st));
-    CU_TRY(cudaStreamSynchronize(st));
+    // rows added earlier may still be in flight on another stream of the caller: growth is rare, wait for the device
+    e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(nx, idx->X, size_t(idx->ntotal) * rowb, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess && nn) e = cudaMemcpyAsync(nn, idx->norm2, size_t(idx->ntotal) * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess && ns) e = cudaMemcpyAsync(ns, idx->Xs, size_t(idx->ntotal) * idx->ld * 2, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+      release_new();
+      return fail(B2R_ERR_CUDA, "copying %lld rows into the grown storage failed: %s", (long long)idx->ntotal, cudaGetErrorString(e));
+    }
   }
   if (idx->X) cudaFree(idx->X);
   if (idx->Xs) cudaFree(idx->Xs);
@@ -275,8 +302,8 @@ extern "C" int b2r_index_add(b2r_index* idx, int64_t n, const float* x, int norm
   if (n < 0) return fail(B2R_ERR_ARG, "negative row count");
   if (n == 0) return B2R_OK;
   if (!x) return fail(B2R_ERR_ARG, "x is null");
-  if (idx->ntotal + n > 0xfffffffeLL) return fail(B2R_ERR_LIMIT, "a shard holds at most 2^32-2 rows");
   std::lock_guard<std::mutex> lk(idx->mu);
+  if (idx->ntotal + n > 0xfffffffeLL) return fail(B2R_ERR_LIMIT, "a shard holds at most 2^32-2 rows");
   DeviceGuard g(idx->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   RC_TRY(grow(idx, idx->ntotal + n, st));
@@ -321,6 +348,7 @@ extern "C" int b2r_index_reset(b2r_index* idx) {
 
 extern "C" int b2r_index_ntotal(const b2r_index* idx, int64_t* out) {
   if (!idx || !out) return fail(B2R_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(const_cast<b2r_index*>(idx)->mu);
   *out = idx->ntotal;
   return B2R_OK;
 }
@@ -332,8 +360,8 @@ __global__ void reconstruct_kernel(const T* row, int d, float* out) {
 
 extern "C" int b2r_index_reconstruct(b2r_index* idx, int64_t i, float* out, void* stream) {
   if (!idx || !out) return fail(B2R_ERR_ARG, "null argument");
-  if (i < 0 || i >= idx->ntotal) return fail(B2R_ERR_ARG, "row %lld out of range (ntotal %lld)", (long long)i, (long long)idx->ntotal);
   std::lock_guard<std::mutex> lk(idx->mu);
+  if (i < 0 || i >= idx->ntotal) return fail(B2R_ERR_ARG, "row %lld out of range (ntotal %lld)", (long long)i, (long long)idx->ntotal);
   DeviceGuard g(idx->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool dev_out = is_device_ptr(out);
@@ -357,6 +385,7 @@ extern "C" int b2r_index_reconstruct(b2r_index* idx, int64_t i, float* out, void
 extern "C" int b2r_index_set_engine(b2r_index* idx, int engine) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
   if (engine < B2R_ENGINE_AUTO || engine > B2R_ENGINE_UMMA3) return fail(B2R_ERR_ARG, "unknown engine %d", engine);
+  std::lock_guard<std::mutex> lk(idx->mu);
   idx->engine = engine;
   return B2R_OK;
 }
@@ -364,6 +393,7 @@ extern "C" int b2r_index_set_engine(b2r_index* idx, int engine) {
 extern "C" int b2r_index_set_shadow(b2r_index* idx, int on) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
   if (idx->storage != B2R_STORE_F32) return fail(B2R_ERR_ARG, "a bf16 shadow only makes sense for fp32 rows (exact mode)");
+  std::lock_guard<std::mutex> lk(idx->mu);
   if (idx->ntotal != 0 || idx->cap_rows != 0) return fail(B2R_ERR_STATE, "set the shadow option before the first add/reserve");
   idx->shadow = on != 0;
   return B2R_OK;
@@ -371,6 +401,7 @@ extern "C" int b2r_index_set_shadow(b2r_index* idx, int on) {
 
 extern "C" int b2r_index_set_verify(b2r_index* idx, int on) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  std::lock_guard<std::mutex> lk(idx->mu);
   idx->verify = on != 0;
   return B2R_OK;
 }
@@ -378,6 +409,7 @@ extern "C" int b2r_index_set_verify(b2r_index* idx, int on) {
 extern "C" int b2r_index_set_pad(b2r_index* idx, int pad) {
   if (!idx) return fail(B2R_ERR_ARG, "index is null");
   if (pad < 0 || pad > 512) return fail(B2R_ERR_ARG, "pad %d out of range (0..512)", pad);
+  std::lock_guard<std::mutex> lk(idx->mu);
   idx->pad = pad;
   return B2R_OK;
 }
@@ -437,28 +469,43 @@ static int launch_fma(b2r_index* idx, int64_t nq, int kp, cudaStream_t st, Final
   return B2R_OK;
 }
 
-// finalize_kernel's dynamic shared memory ((sortn + K'2) * 8 <= 48 KiB + its static arrays) needs the opt-in
-// attribute; it is set to a fixed 64 KiB once per device and kernel instance, never lowered.
-static int finalize_smem_once(int device, int which) {
+// Kernels whose dynamic shared memory can exceed the 48 KiB default need the opt-in attribute; it is set to a
+// fixed size once per device and kernel instance, never lowered (other handles may be launching).
+enum { kAttrFinalize = 0, kAttrRange = 2, kAttrExact = 4, kAttrMerge = 6, kAttrCount = 7 };
+constexpr size_t kFinalizeSmemMax = 64 * 1024, kExactSmemMax = 160 * 1024;
+static int smem_attr_once(int device, int which) {
   static std::mutex mu;
-  static bool done[64][2] = {};
+  static bool done[64][kAttrCount] = {};
   std::lock_guard<std::mutex> lk(mu);
   if (device < 0 || device >= 64) return fail(B2R_ERR_ARG, "device %d out of range", device);
   if (done[device][which]) return B2R_OK;
-  if (which)
-    CU_TRY(cudaFuncSetAttribute(finalize_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  else
-    CU_TRY(cudaFuncSetAttribute(finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  switch (which) {
+    case kAttrFinalize + 0: CU_TRY(cudaFuncSetAttribute(finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFinalizeSmemMax))); break;
+    case kAttrFinalize + 1: CU_TRY(cudaFuncSetAttribute(finalize_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFinalizeSmemMax))); break;
+    case kAttrRange + 0: CU_TRY(cudaFuncSetAttribute(finalize_range_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFinalizeSmemMax))); break;
+    case kAttrRange + 1: CU_TRY(cudaFuncSetAttribute(finalize_range_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFinalizeSmemMax))); break;
+    case kAttrExact + 0: CU_TRY(cudaFuncSetAttribute(score_exact_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kExactSmemMax))); break;
+    case kAttrExact + 1: CU_TRY(cudaFuncSetAttribute(score_exact_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kExactSmemMax))); break;
+    case kAttrMerge: CU_TRY(cudaFuncSetAttribute(merge_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFinalizeSmemMax))); break;
+    default: return fail(B2R_ERR_ARG, "unknown kernel %d", which);
+  }
   done[device][which] = true;
   return B2R_OK;
 }
 
+constexpr int kRangeKeep = 2048;   // most candidates finalize_range_kernel re-scores per query
+constexpr int kFbHeader = 16;      // counters in front of the hand-over lists
+
+// One batch (<= 8192 queries), device pointers only, everything enqueued on `st`, nothing read back:
+//   prep -> first pass (tcgen05 seed/select/main, or FMA) -> finalize (+ proof, hand-over lists)
+//        -> [range pass -> finalize_range] -> exhaustive scan of whatever is still unproven.
+// The last three launches return at once when their list is empty.
 static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t k, int normalize_queries,
-                         int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st, int force_engine) {
+                         int64_t row_offset, float* D, int64_t* I, uint64_t* packed, cudaStream_t st, bool clear_stats) {
   // engine and K'.  The 1xTF32 tensor-core pass truncates both operands to 10 mantissa bits, so it keeps a wider
   // candidate list (K' >= 2k, at least k + 22) for the completeness proof to go through; FMA, bf16 (exact
   // products) and 3xTF32 keep k + pad.  The pad grows with k: gaps between neighbouring scores shrink like 1/rank.
-  const int engine = force_engine ? force_engine : idx->engine;
+  const int engine = idx->engine;
   bool use_umma = false, split = false, use_shadow = false;
   int kp = int(std::min<int64_t>(k + std::max<int64_t>(idx->pad, k / 8), 2048));
   if (idx->ntotal > 0 && engine != B2R_ENGINE_FMA) {
@@ -476,6 +523,11 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
       return fail(B2R_ERR_LIMIT, "the tcgen05 engine does not take this shape (storage %d, d %lld, k' %d)", idx->storage, (long long)idx->d, kp_tc);
     if (!use_umma) { split = false; use_shadow = false; }
   }
+  const bool f32 = idx->storage == B2R_STORE_F32;
+  // unproven queries are handed on (device side) when the proof can fail at all: rows may only be filtered out
+  // when there are more of them than K'
+  const bool chain = idx->verify && idx->ntotal > kp;
+  const bool range_ok = chain && use_umma;
   int launches = 0;
   const int ldq = idx->ld;
   RC_TRY(idx->qf.ensure(size_t(nq + 256) * ldq * 4));
@@ -483,25 +535,36 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   if (split) RC_TRY(idx->qlo.ensure(size_t(nq + 256) * ldq * 4));
   RC_TRY(idx->qn2.ensure(size_t(nq) * 4));
   RC_TRY(idx->thr.ensure(size_t(nq) * 4));
-  RC_TRY(idx->stats.ensure(2 * sizeof(unsigned long long)));
+  RC_TRY(idx->stats.ensure(4 * sizeof(unsigned long long)));
+  RC_TRY(idx->fb.ensure(size_t(kFbHeader + 4 * nq) * 4));
+  if (range_ok) {
+    if (f32) {
+      RC_TRY(idx->qc_f.ensure(size_t(nq + 256) * ldq * 4));
+      RC_TRY(idx->qc_lo.ensure(size_t(nq + 256) * ldq * 4));
+    } else {
+      RC_TRY(idx->qc_h.ensure(size_t(nq + 256) * ldq * 2));
+    }
+  }
+  uint32_t* fb = static_cast<uint32_t*>(idx->fb.p);
   {
     const int blocks = int(std::min<int64_t>((nq + 7) / 8, int64_t(idx->sm_count) * 8));
     prep_queries_kernel<<<blocks, 256, 0, st>>>(q_dev, nq, int(idx->d), ldq, normalize_queries,
                                                 idx->storage == B2R_STORE_BF16, static_cast<float*>(idx->qf.p),
                                                 (idx->storage == B2R_STORE_BF16 || use_shadow) ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
                                                 static_cast<float*>(idx->qn2.p), split ? static_cast<float*>(idx->qlo.p) : nullptr,
-                                                static_cast<uint32_t*>(idx->thr.p), static_cast<unsigned long long*>(idx->stats.p));
+                                                static_cast<uint32_t*>(idx->thr.p),
+                                                clear_stats ? static_cast<unsigned long long*>(idx->stats.p) : nullptr, fb);
     CU_TRY(cudaGetLastError());
     ++launches;
   }
   FinalizeParams fp{};
   int engine_used = B2R_ENGINE_FMA;
   int64_t main_rows = idx->ntotal;
+  UmmaCall uc{};
   if (idx->ntotal > 0) {
     const int slot = int(idx->nrec % b2r_index::kEvPool);
     if (!use_umma) CU_TRY(cudaEventRecord(idx->ev0[slot], st));
     if (use_umma) {
-      UmmaCall uc{};
       uc.X = use_shadow ? idx->Xs : idx->X; uc.n = idx->ntotal; uc.ld = idx->ld; uc.d = int(idx->d);
       uc.storage = use_shadow ? B2R_STORE_BF16 : idx->storage;
       uc.shadow = use_shadow;
@@ -542,37 +605,87 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   fp.maxnorm2 = idx->maxnorm2;
   fp.D = D; fp.I = I; fp.packed = packed;
   fp.stats = static_cast<unsigned long long*>(idx->stats.p);
-  const size_t smem = size_t(fp.sortn + host_next_pow2(kp)) * 8;
-  if (idx->storage == B2R_STORE_BF16) {
-    RC_TRY(finalize_smem_once(idx->device, 1));
-    finalize_kernel<__nv_bfloat16><<<int(nq), fin_threads, smem, st>>>(fp);
-  } else {
-    RC_TRY(finalize_smem_once(idx->device, 0));
-    finalize_kernel<float><<<int(nq), fin_threads, smem, st>>>(fp);
+  if (chain) {
+    fp.fb = fb;
+    fp.fb_q1 = fb + kFbHeader; fp.fb_thr1 = fb + kFbHeader + nq; fp.fb_ovf = fb + kFbHeader + 2 * nq; fp.fb_q2 = fb + kFbHeader + 3 * nq;
+    fp.range_ok = range_ok ? 1 : 0;
+    fp.range_keep = kRangeKeep;
+    if (range_ok) {
+      // the range pass runs the most accurate tensor-core variant the rows allow: 3xTF32 on fp32 rows, kind::f16 on bf16 rows
+      fp.errfac_range = umma_errfac(f32, f32, false, int(idx->d));
+      fp.qc_f = f32 ? static_cast<float*>(idx->qc_f.p) : nullptr;
+      fp.qc_lo = f32 ? static_cast<float*>(idx->qc_lo.p) : nullptr;
+      fp.qc_h = f32 ? nullptr : static_cast<__nv_bfloat16*>(idx->qc_h.p);
+    }
   }
+  const size_t smem = size_t(fp.sortn + host_next_pow2(kp)) * 8;
+  RC_TRY(smem_attr_once(idx->device, kAttrFinalize + (f32 ? 0 : 1)));
+  if (f32) finalize_kernel<float><<<int(nq), fin_threads, smem, st>>>(fp);
+  else finalize_kernel<__nv_bfloat16><<<int(nq), fin_threads, smem, st>>>(fp);
   CU_TRY(cudaGetLastError());
   ++launches;
-  idx->last = b2r_search_stats{};
-  idx->last_is_sum = false;
-  idx->last.nq = nq; idx->last.k = k; idx->last.kprime = kp;
-  idx->last.engine = engine_used; idx->last.launches = launches; idx->last.main_rows = main_rows;
+
+  if (chain) {
+    if (range_ok) {
+      UmmaCall rc_call{};
+      rc_call.X = idx->X; rc_call.n = idx->ntotal; rc_call.ld = idx->ld; rc_call.d = int(idx->d);
+      rc_call.storage = idx->storage;
+      rc_call.Qh = idx->qc_h.p; rc_call.Qf = static_cast<const float*>(idx->qc_f.p); rc_call.Qlo = static_cast<const float*>(idx->qc_lo.p);
+      rc_call.nq = int(nq); rc_call.kp = kp;
+      rc_call.norm2 = uc.norm2; rc_call.thr = fp.fb_thr1; rc_call.sm_count = idx->sm_count;
+      rc_call.split = f32;
+      rc_call.list_len = fb; rc_call.ovf = fp.fb_ovf;
+      FinalizeParams rp = fp;
+      std::string err;
+      int rc = umma_launch_range(idx->umma, rc_call, uc, st, rp, &launches, err);
+      if (rc != B2R_OK) return fail(rc, "%s", err.c_str());
+      rp.sortn = 2 * kRangeKeep;
+      const size_t rsmem = size_t(rp.sortn + kRangeKeep) * 8;
+      RC_TRY(smem_attr_once(idx->device, kAttrRange + (f32 ? 0 : 1)));
+      const int rgrid = int(std::min<int64_t>(nq, int64_t(idx->sm_count) * 2));
+      if (f32) finalize_range_kernel<float><<<rgrid, kFinThreads, rsmem, st>>>(rp);
+      else finalize_range_kernel<__nv_bfloat16><<<rgrid, kFinThreads, rsmem, st>>>(rp);
+      CU_TRY(cudaGetLastError());
+      ++launches;
+    }
+    // exhaustive DOT64 scan of whatever is still unproven (cooperative: its CTAs meet at a grid barrier)
+    FinalizeParams xp = fp;
+    xp.sortn = std::max(4096, host_next_pow2(int(k) + 2048));
+    int cap = 128;
+    while (cap < int(k) + 64) cap <<= 1;
+    const size_t xsmem = std::max(size_t(kExQB) * cap * 8, size_t(xp.sortn + host_next_pow2(int(k))) * 8);
+    const int w = f32 ? 0 : 1;
+    RC_TRY(smem_attr_once(idx->device, kAttrExact + w));
+    if (idx->exact_occ[w] == 0 || idx->exact_occ_smem[w] != xsmem) {
+      int occ = 0;
+      if (f32) CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, score_exact_kernel<float>, kExThreads, xsmem));
+      else CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, score_exact_kernel<__nv_bfloat16>, kExThreads, xsmem));
+      if (occ < 1) return fail(B2R_ERR_LIMIT, "the exhaustive scan does not fit an SM (k=%lld)", (long long)k);
+      idx->exact_occ[w] = std::min(occ, 2);
+      idx->exact_occ_smem[w] = xsmem;
+    }
+    const int xgrid = idx->sm_count * idx->exact_occ[w];
+    int64_t wave = (int64_t(32) << 20) / (int64_t(xgrid) * k * 8) / kExQB * kExQB;
+    wave = std::max<int64_t>(kExQB, std::min<int64_t>(wave, (nq + kExQB - 1) / kExQB * kExQB));
+    RC_TRY(idx->exl.ensure(size_t(wave) * xgrid * k * 8));
+    uint64_t* lists = static_cast<uint64_t*>(idx->exl.p);
+    int wave_i = int(wave);
+    void* args[] = {&xp, &lists, &wave_i, &cap};
+    if (f32) CU_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(score_exact_kernel<float>), dim3(xgrid), dim3(kExThreads), args, xsmem, st));
+    else CU_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(score_exact_kernel<__nv_bfloat16>), dim3(xgrid), dim3(kExThreads), args, xsmem, st));
+    ++launches;
+  }
+  if (clear_stats) {
+    idx->last = b2r_search_stats{};
+    idx->last.launches = 0;
+  }
+  idx->last.nq += nq; idx->last.k = k; idx->last.kprime = kp;
+  idx->last.engine = engine_used; idx->last.launches += launches; idx->last.main_rows = main_rows;
   return B2R_OK;
 }
 
 static int search_batch(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries, int64_t row_offset,
-                        float* D, int64_t* I, uint64_t* packed, void* stream, uint64_t* flag_out = nullptr) {
-  if (!idx) return fail(B2R_ERR_ARG, "index is null");
-  if (nq < 0) return fail(B2R_ERR_ARG, "negative query count");
-  if (k <= 0) return fail(B2R_ERR_ARG, "k must be positive (got %lld)", (long long)k);
-  if (k > 1024) return fail(B2R_ERR_LIMIT, "k=%lld exceeds the supported maximum of 1024", (long long)k);
-  if (nq == 0) return B2R_OK;
-  if (nq > (int64_t(1) << 22)) return fail(B2R_ERR_LIMIT, "at most 2^22 queries per call");
-  if (!q) return fail(B2R_ERR_ARG, "q is null");
-  if (packed ? false : (!D || !I)) return fail(B2R_ERR_ARG, "D or I is null");
-  if (idx->ntotal + row_offset > 0xfffffffeLL || row_offset < 0) return fail(B2R_ERR_LIMIT, "global ids must stay below 2^32-1");
-  std::lock_guard<std::mutex> lk(idx->mu);
-  DeviceGuard g(idx->device);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+                        float* D, int64_t* I, uint64_t* packed, cudaStream_t st, bool first_batch) {
   const bool q_dev = is_device_ptr(q);
   const bool out_dev = packed ? true : is_device_ptr(D);
   if (!packed && out_dev != is_device_ptr(I)) return fail(B2R_ERR_ARG, "D and I must both be host or both be device pointers");
@@ -585,72 +698,52 @@ static int search_batch(b2r_index* idx, int64_t nq, const float* q, int64_t k, i
   }
   float* Dd = D;
   int64_t* Id = I;
-  if (!packed && !out_dev) {
+  const bool host_out = !packed && !out_dev;
+  if (host_out) {
     RC_TRY(idx->stage_d.ensure(size_t(nq) * k * 4));
     RC_TRY(idx->stage_i.ensure(size_t(nq) * k * 8));
     Dd = static_cast<float*>(idx->stage_d.p);
     Id = static_cast<int64_t*>(idx->stage_i.p);
   }
-  RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, 0));
-  idx->last.fallback = 0;
-  const bool host_out = !packed && !out_dev;
-  auto copy_back = [&]() -> int {   // results (and the proof counter) to the host, one sync
-    if (host_out) {
-      CU_TRY(cudaMemcpyAsync(D, Dd, size_t(nq) * k * 4, cudaMemcpyDeviceToHost, st));
-      CU_TRY(cudaMemcpyAsync(I, Id, size_t(nq) * k * 8, cudaMemcpyDeviceToHost, st));
-    }
-    return B2R_OK;
-  };
-  if (flag_out)   // deferred proof: the caller reads the unverified count later (it rides in its all-gather payload)
-    CU_TRY(cudaMemcpyAsync(flag_out, idx->stats.p, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
-  const bool check_proof = (idx->last.engine == B2R_ENGINE_UMMA || idx->last.engine == B2R_ENGINE_SHADOW) &&
-                           idx->storage == B2R_STORE_F32 && idx->verify && !flag_out;
-  if (check_proof) {
-    // exact mode on the tensor cores is only as good as its proof: read the counter of unproven queries and, if
-    // any, search again with the 3xTF32 split (error bound ~30x tighter; FMA engine where tcgen05 cannot take the
-    // shape).  Host-buffer callers pay nothing extra (the counter rides with the results); device-pointer callers
-    // pay one stream sync per search.
-    RC_TRY(copy_back());
-    CU_TRY(cudaMemcpyAsync(idx->host_flag, idx->stats.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    CU_TRY(cudaStreamSynchronize(st));
-    if (*idx->host_flag != 0ull) {
-      const int l0 = idx->last.launches;
-      const int kp3 = int(k + std::max<int64_t>(idx->pad, k / 8));
-      const int fb = umma_supported(idx->storage, int(idx->d), kp3, idx->ntotal) ? B2R_ENGINE_UMMA3 : B2R_ENGINE_FMA;
-      RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, fb));
-      idx->last.fallback = 1;
-      idx->last.launches += l0;
-      RC_TRY(copy_back());
-      if (host_out || !q_dev) CU_TRY(cudaStreamSynchronize(st));
-    }
-  } else {
-    RC_TRY(copy_back());
-    if (host_out || !q_dev) CU_TRY(cudaStreamSynchronize(st));   // results in host memory / host query buffer reusable
+  RC_TRY(search_device(idx, nq, qd, k, normalize_queries, row_offset, Dd, Id, packed, st, first_batch));
+  if (host_out) {
+    CU_TRY(cudaMemcpyAsync(D, Dd, size_t(nq) * k * 4, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(I, Id, size_t(nq) * k * 8, cudaMemcpyDeviceToHost, st));
   }
+  // host buffers: the results must be there (and the query buffer reusable) on return; device pointers: enqueue only
+  if (host_out || !q_dev) CU_TRY(cudaStreamSynchronize(st));
   return B2R_OK;
 }
 
-// Large query sets go through in batches of 8192 queries so that the candidate scratch stays bounded
-// (the corpus is streamed once per 2048 queries either way).
+static int check_search_args(b2r_index* idx, int64_t nq, const float* q, int64_t k) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (nq < 0) return fail(B2R_ERR_ARG, "negative query count");
+  if (k <= 0) return fail(B2R_ERR_ARG, "k must be positive (got %lld)", (long long)k);
+  if (k > 1024) return fail(B2R_ERR_LIMIT, "k=%lld exceeds the supported maximum of 1024", (long long)k);
+  if (nq > (int64_t(1) << 22)) return fail(B2R_ERR_LIMIT, "at most 2^22 queries per call");
+  if (nq > 0 && !q) return fail(B2R_ERR_ARG, "q is null");
+  return B2R_OK;
+}
+
+// Large query sets go through in batches of 8192 queries so that the candidate scratch stays bounded (the corpus is
+// streamed once per 2048 queries either way).  The counters of the batches add up on the device.
+constexpr int64_t kSearchBatch = 8192;
 static int search_any(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries, int64_t row_offset,
                       float* D, int64_t* I, uint64_t* packed, void* stream) {
-  constexpr int64_t kBatch = 8192;
-  if (!idx || nq <= kBatch || !q || k <= 0 || k > 1024)
-    return search_batch(idx, nq, q, k, normalize_queries, row_offset, D, I, packed, stream);
-  b2r_search_stats total{};
-  for (int64_t q0 = 0; q0 < nq; q0 += kBatch) {
-    const int64_t m = std::min(kBatch, nq - q0);
-    RC_TRY(search_batch(idx, m, q + q0 * idx->d, k, normalize_queries, row_offset, D ? D + q0 * k : nullptr,
-                        I ? I + q0 * k : nullptr, packed ? packed + q0 * k : nullptr, stream));
-    b2r_search_stats st;
-    RC_TRY(b2r_index_last_stats(idx, &st));      // per-batch counters are summed (synchronises)
-    total.nq += st.nq; total.unverified += st.unverified; total.candidates += st.candidates;
-    total.launches += st.launches; total.fallback |= st.fallback;
-    total.k = st.k; total.kprime = st.kprime; total.engine = st.engine; total.main_rows = st.main_rows;
-  }
+  RC_TRY(check_search_args(idx, nq, q, k));
+  if (nq == 0) return B2R_OK;
+  if (packed ? false : (!D || !I)) return fail(B2R_ERR_ARG, "D or I is null");
   std::lock_guard<std::mutex> lk(idx->mu);
-  idx->last = total;
-  idx->last_is_sum = true;
+  if (idx->ntotal + row_offset > 0xfffffffeLL || row_offset < 0) return fail(B2R_ERR_LIMIT, "global ids must stay below 2^32-1");
+  DeviceGuard g(idx->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (int64_t q0 = 0; q0 < nq; q0 += kSearchBatch) {
+    const int64_t m = std::min(kSearchBatch, nq - q0);
+    RC_TRY(search_batch(idx, m, q + q0 * idx->d, k, normalize_queries, row_offset, D ? D + q0 * k : nullptr,
+                        I ? I + q0 * k : nullptr, packed ? packed + q0 * k : nullptr, st, q0 == 0));
+  }
+  idx->searched = true;
+  CU_TRY(cudaEventRecord(idx->ev_done, st));
   return B2R_OK;
 }
 
@@ -667,20 +760,13 @@ extern "C" int b2r_index_search_packed(b2r_index* idx, int64_t nq, const float* 
   return search_any(idx, nq, q, k, normalize_queries, row_offset, nullptr, nullptr, packed, stream);
 }
 
-extern "C" int b2r_index_search_packed_async(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries,
-                                             int64_t row_offset, uint64_t* packed, void* stream) {
-  if (!packed) return fail(B2R_ERR_ARG, "packed is null");
-  if (nq > 8192) return fail(B2R_ERR_LIMIT, "b2r_index_search_packed_async takes at most 8192 queries per call");
-  if (nq <= 0 || k <= 0) return fail(B2R_ERR_ARG, "bad shape nq=%lld k=%lld", (long long)nq, (long long)k);
-  return search_batch(idx, nq, q, k, normalize_queries, row_offset, nullptr, nullptr, packed, stream, packed + nq * k);
-}
-
-extern "C" int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed,
-                                        int64_t g_stride, float* D, int64_t* I, int device, void* stream);
-
-extern "C" int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed, float* D,
-                                int64_t* I, int device, void* stream) {
-  return b2r_merge_packed_strided(metric, G, nq, k, packed, nq * k, D, I, device, stream);
+static int merge_launch(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed, int64_t g_stride, float* D,
+                        int64_t* I, int device, cudaStream_t st) {
+  const int sortn = std::max(4096, host_next_pow2(int(k) + 2048));   // gather rounds append up to 2048 keys
+  RC_TRY(smem_attr_once(device, kAttrMerge));
+  merge_packed_kernel<<<int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st>>>(packed, int(G), int(nq), int(k), g_stride, sortn, metric, D, I);
+  CU_TRY(cudaGetLastError());
+  return B2R_OK;
 }
 
 extern "C" int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed,
@@ -689,32 +775,39 @@ extern "C" int b2r_merge_packed_strided(int metric, int64_t G, int64_t nq, int64
   if (metric != B2R_METRIC_IP && metric != B2R_METRIC_L2) return fail(B2R_ERR_ARG, "unknown metric %d", metric);
   if (G <= 0 || nq < 0 || k <= 0) return fail(B2R_ERR_ARG, "bad shape G=%lld nq=%lld k=%lld", (long long)G, (long long)nq, (long long)k);
   if (k > 1024) return fail(B2R_ERR_LIMIT, "k=%lld exceeds the supported maximum of 1024", (long long)k);
+  if (G > kFinMaxSlots) return fail(B2R_ERR_LIMIT, "at most %d lists can be merged (got %lld)", kFinMaxSlots, (long long)G);
   if (nq == 0) return B2R_OK;
   if (!packed || !D || !I) return fail(B2R_ERR_ARG, "null argument");
   if (b2r_device_count() <= 0) return fail(B2R_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
   if (!is_device_ptr(packed) || !is_device_ptr(D) || !is_device_ptr(I)) return fail(B2R_ERR_ARG, "packed, D and I must be device pointers");
   DeviceGuard g(device);
   if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int sortn = std::max(4096, host_next_pow2(int(k) + 2048));   // gather rounds append up to 2048 keys
-  merge_packed_kernel<<<int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st>>>(packed, int(G), int(nq), int(k), g_stride, sortn, metric, D, I);
-  CU_TRY(cudaGetLastError());
-  return B2R_OK;
+  return merge_launch(metric, G, nq, k, packed, g_stride, D, I, device, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int b2r_merge_packed(int metric, int64_t G, int64_t nq, int64_t k, const uint64_t* packed, float* D,
+                                int64_t* I, int device, void* stream) {
+  return b2r_merge_packed_strided(metric, G, nq, k, packed, nq * k, D, I, device, stream);
 }
 
 extern "C" int b2r_index_last_stats(b2r_index* idx, b2r_search_stats* out) {
   if (!idx || !out) return fail(B2R_ERR_ARG, "null argument");
   std::lock_guard<std::mutex> lk(idx->mu);
   DeviceGuard g(idx->device);
-  unsigned long long h[2] = {0, 0};
-  if (idx->stats.p) {
-    CU_TRY(cudaDeviceSynchronize());
-    CU_TRY(cudaMemcpy(h, idx->stats.p, sizeof h, cudaMemcpyDeviceToHost));
+  unsigned long long h[4] = {0, 0, 0, 0};
+  if (idx->stats.p && idx->searched) {
+    // wait for the most recent search only (its last kernel recorded ev_done), then read the four counters
+    CU_TRY(cudaEventSynchronize(idx->ev_done));
+    CU_TRY(cudaMemcpyAsync(h, idx->stats.p, sizeof h, cudaMemcpyDeviceToHost, idx->side));
+    CU_TRY(cudaStreamSynchronize(idx->side));
   }
-  if (!idx->last_is_sum) {   // a batched call already summed its per-batch counters
-    idx->last.unverified = int64_t(h[0]);
-    idx->last.candidates = int64_t(h[1]);
-  }
+  // with the hand-over on (default) every unproven query ends in the exhaustive scan at the latest, so none is left
+  // unverified; with b2r_index_set_verify(idx, 0) the first pass's unproven queries are only counted
+  idx->last.fallback_queries = idx->verify ? int64_t(h[0]) : 0;
+  idx->last.candidates = int64_t(h[1]);
+  idx->last.exhaustive_queries = int64_t(h[2]);
+  idx->last.unverified = int64_t(h[3]);
+  idx->last.fallback = idx->last.fallback_queries != 0 ? 1 : 0;
   *out = idx->last;
   return B2R_OK;
 }
@@ -747,6 +840,155 @@ extern "C" int b2r_index_score_time(b2r_index* idx, int reset, double* total_ms,
   if (total_ms) *total_ms = sum;
   if (nsearch) *nsearch = cnt;
   if (reset) { idx->nrec = 0; idx->have_times = false; }
+  return B2R_OK;
+}
+
+// --------------------------------------------------------------------------------------
+// row-sharded search: one NCCL all-gather of the packed shard-local top-k, then the merge kernel
+// --------------------------------------------------------------------------------------
+// NCCL is bound at run time (dlopen): the library that is already loaded in the process wins (so a communicator
+// created by the host framework's NCCL and one created here come from the same instance), else libnccl.so.2 from
+// the loader path.  Only the five entry points below are used; their types are restated to keep nccl.h out of the
+// build.
+typedef struct { char internal[128]; } b2r_nccl_uid;
+struct NcclApi {
+  void* h = nullptr;
+  int (*GetUniqueId)(b2r_nccl_uid*) = nullptr;
+  int (*CommInitRank)(void**, int, b2r_nccl_uid, int) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+static NcclApi* nccl_api() {
+  static std::mutex mu;
+  static NcclApi api;
+  static bool tried = false;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!tried) {
+    tried = true;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (h) {
+      api.GetUniqueId = reinterpret_cast<int (*)(b2r_nccl_uid*)>(dlsym(h, "ncclGetUniqueId"));
+      api.CommInitRank = reinterpret_cast<int (*)(void**, int, b2r_nccl_uid, int)>(dlsym(h, "ncclCommInitRank"));
+      api.CommDestroy = reinterpret_cast<int (*)(void*)>(dlsym(h, "ncclCommDestroy"));
+      api.AllGather = reinterpret_cast<int (*)(const void*, void*, size_t, int, void*, cudaStream_t)>(dlsym(h, "ncclAllGather"));
+      api.GetErrorString = reinterpret_cast<const char* (*)(int)>(dlsym(h, "ncclGetErrorString"));
+      if (api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GetErrorString) api.h = h;
+    }
+  }
+  return api.h ? &api : nullptr;
+}
+constexpr int kNcclUint64 = 5;   // ncclDataType_t ncclUint64
+
+static void comm_release(b2r_index* idx) {
+  if (idx->comm && idx->comm_owned) {
+    NcclApi* n = nccl_api();
+    if (n) n->CommDestroy(idx->comm);
+  }
+  idx->comm = nullptr;
+  idx->comm_owned = false;
+  idx->rank = 0;
+  idx->world = 1;
+  idx->row_offset = 0;
+}
+
+extern "C" int b2r_nccl_unique_id(void* out128) {
+  if (!out128) return fail(B2R_ERR_ARG, "out is null");
+  NcclApi* n = nccl_api();
+  if (!n) return fail(B2R_ERR_STATE, "the NCCL library (libnccl.so.2) could not be loaded");
+  b2r_nccl_uid id;
+  const int r = n->GetUniqueId(&id);
+  if (r != 0) return fail(B2R_ERR_CUDA, "ncclGetUniqueId failed: %s", n->GetErrorString(r));
+  memcpy(out128, &id, sizeof id);
+  return B2R_OK;
+}
+
+static int comm_check(b2r_index* idx, int rank, int world, int64_t row_offset) {
+  if (!idx) return fail(B2R_ERR_ARG, "index is null");
+  if (world < 1 || world > kFinMaxSlots || rank < 0 || rank >= world) return fail(B2R_ERR_ARG, "bad rank %d of %d", rank, world);
+  if (row_offset < 0) return fail(B2R_ERR_ARG, "negative row offset");
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_set_comm(b2r_index* idx, void* nccl_comm, int rank, int world, int64_t row_offset) {
+  RC_TRY(comm_check(idx, rank, world, row_offset));
+  if (world > 1 && !nccl_comm) return fail(B2R_ERR_ARG, "nccl_comm is null");
+  if (world > 1 && !nccl_api()) return fail(B2R_ERR_STATE, "the NCCL library (libnccl.so.2) could not be loaded");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  comm_release(idx);
+  idx->comm = world > 1 ? nccl_comm : nullptr;
+  idx->comm_owned = false;
+  idx->rank = rank; idx->world = world; idx->row_offset = row_offset;
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_comm_init(b2r_index* idx, const void* unique_id128, int rank, int world, int64_t row_offset) {
+  RC_TRY(comm_check(idx, rank, world, row_offset));
+  if (world > 1 && !unique_id128) return fail(B2R_ERR_ARG, "unique id is null");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  comm_release(idx);
+  if (world > 1) {
+    NcclApi* n = nccl_api();
+    if (!n) return fail(B2R_ERR_STATE, "the NCCL library (libnccl.so.2) could not be loaded");
+    DeviceGuard g(idx->device);
+    b2r_nccl_uid id;
+    memcpy(&id, unique_id128, sizeof id);
+    void* comm = nullptr;
+    const int r = n->CommInitRank(&comm, world, id, rank);
+    if (r != 0) return fail(B2R_ERR_CUDA, "ncclCommInitRank failed: %s", n->GetErrorString(r));
+    idx->comm = comm;
+    idx->comm_owned = true;
+  }
+  idx->rank = rank; idx->world = world; idx->row_offset = row_offset;
+  return B2R_OK;
+}
+
+extern "C" int b2r_index_search_sharded(b2r_index* idx, int64_t nq, const float* q, int64_t k, int normalize_queries,
+                                        float* D, int64_t* I, void* stream) {
+  RC_TRY(check_search_args(idx, nq, q, k));
+  if (nq == 0) return B2R_OK;
+  if (!D || !I) return fail(B2R_ERR_ARG, "D or I is null");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  if (idx->world > 1 && !idx->comm) return fail(B2R_ERR_STATE, "no communicator: call b2r_index_set_comm or b2r_index_comm_init first");
+  if (idx->ntotal + idx->row_offset > 0xfffffffeLL) return fail(B2R_ERR_LIMIT, "global ids must stay below 2^32-1");
+  NcclApi* n = idx->world > 1 ? nccl_api() : nullptr;
+  DeviceGuard g(idx->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool out_dev = is_device_ptr(D);
+  if (out_dev != is_device_ptr(I)) return fail(B2R_ERR_ARG, "D and I must both be host or both be device pointers");
+  const int64_t mb = std::min(nq, kSearchBatch);
+  // handle-owned, persistent: this rank's packed top-k and the gathered [world][batch*k] lists
+  RC_TRY(idx->shard_local.ensure(size_t(mb) * k * 8));
+  RC_TRY(idx->shard_all.ensure(size_t(idx->world) * mb * k * 8));
+  if (!out_dev) {
+    RC_TRY(idx->stage_d.ensure(size_t(mb) * k * 4));
+    RC_TRY(idx->stage_i.ensure(size_t(mb) * k * 8));
+  }
+  uint64_t* local = static_cast<uint64_t*>(idx->shard_local.p);
+  uint64_t* all = static_cast<uint64_t*>(idx->shard_all.p);
+  for (int64_t q0 = 0; q0 < nq; q0 += kSearchBatch) {
+    const int64_t m = std::min(kSearchBatch, nq - q0);
+    RC_TRY(search_batch(idx, m, q + q0 * idx->d, k, normalize_queries, idx->row_offset, nullptr, nullptr, local, st, q0 == 0));
+    const uint64_t* lists = local;
+    if (idx->world > 1) {
+      const int r = n->AllGather(local, all, size_t(m) * k, kNcclUint64, idx->comm, st);   // the single collective
+      if (r != 0) return fail(B2R_ERR_CUDA, "ncclAllGather failed: %s", n->GetErrorString(r));
+      lists = all;
+    }
+    float* Dd = out_dev ? D + q0 * k : static_cast<float*>(idx->stage_d.p);
+    int64_t* Id = out_dev ? I + q0 * k : static_cast<int64_t*>(idx->stage_i.p);
+    RC_TRY(merge_launch(idx->metric, idx->world, m, k, lists, m * k, Dd, Id, idx->device, st));
+    ++idx->last.launches;
+    if (!out_dev) {
+      CU_TRY(cudaMemcpyAsync(D + q0 * k, Dd, size_t(m) * k * 4, cudaMemcpyDeviceToHost, st));
+      CU_TRY(cudaMemcpyAsync(I + q0 * k, Id, size_t(m) * k * 8, cudaMemcpyDeviceToHost, st));
+      CU_TRY(cudaStreamSynchronize(st));
+    }
+  }
+  idx->searched = true;
+  CU_TRY(cudaEventRecord(idx->ev_done, st));
   return B2R_OK;
 }
 
@@ -861,8 +1103,19 @@ extern "C" int b2r_cosine_rows_noalloc(int64_t n, int64_t m, int64_t d, const fl
   const int ndev = b2r_device_count();
   if (ndev <= 0) return fail(B2R_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
   if (device < 0 || device >= ndev || device >= 64) return fail(B2R_ERR_ARG, "device %d out of range", device);
-  if (!is_device_ptr(resp) || !is_device_ptr(maxcos) || (m > 0 && !is_device_ptr(docs)) || (cosout && !is_device_ptr(cosout)))
-    return fail(B2R_ERR_ARG, "b2r_cosine_rows_noalloc takes device pointers only (staging host buffers would need an allocation)");
+  {
+    // every buffer must be device memory of `device` itself: a pointer owned by another GPU would fault in the
+    // kernel (no peer mapping is set up here), so it is refused up front
+    const void* ptrs[4] = {resp, maxcos, m > 0 ? docs : nullptr, cosout};
+    for (const void* ptr : ptrs) {
+      if (!ptr) continue;
+      int owner = -1;
+      if (!is_device_ptr(ptr, &owner))
+        return fail(B2R_ERR_ARG, "b2r_cosine_rows_noalloc takes device pointers only (staging host buffers would need an allocation)");
+      if (owner != device)
+        return fail(B2R_ERR_ARG, "a buffer lives on device %d but the call names device %d", owner, device);
+    }
+  }
   DeviceGuard g(device);
   if (!g.ok) return fail(B2R_ERR_CUDA, "cudaSetDevice(%d) failed", device);
   uint32_t* scratch = nullptr;

@@ -11,11 +11,18 @@
 //      the cross-GPU all-gather);
 //   4. proves completeness: if fl32(a_min + E) is strictly worse than the k-th returned score,
 //      no row that the scoring pass filtered out can belong to the top-k.
+//   5. a query whose proof fails is handed on, on the device, to the second pass: its index, its prepared row
+//      and the fixed threshold T = s_k - E' (E' = error bound of the range pass) go to a compact list; the
+//      range pass (score_umma.cuh, range mode) collects EVERY row whose approximate score reaches T — a
+//      superset of the true top-k that needs no gap — and finalize_range_kernel re-scores and orders it.
+//      If that set does not fit its buffers (thousands of rows tied with the k-th score) the query goes on
+//      to the exhaustive DOT64 scan (score_exact.cuh), which cannot fail.  No host round trip anywhere.
 // The same gather merges the all-gathered [G,nq,k] packed lists (merge_packed_kernel) and selects the seed
 // thresholds of the tcgen05 engine (seed_select_kernel in score_umma.cuh).
 #pragma once
 #include <float.h>
 #include "common.cuh"
+#include "prep.cuh"
 
 namespace b2r {
 
@@ -40,7 +47,20 @@ struct FinalizeParams {
   int metric; int64_t n; int64_t row_offset;
   float errfac; const float* maxnorm2;
   float* D; int64_t* I; uint64_t* packed;
-  unsigned long long* stats;  // [0] unverified queries, [1] candidates seen
+  unsigned long long* stats;  // [0] queries unproven by the first pass, [1] candidates seen,
+                              // [2] queries sent on to the exhaustive scan, [3] queries left unproven
+  // hand-over of unproven queries (all optional: fb == nullptr keeps the counters only)
+  uint32_t* fb;            // [0] entries of the range list, [1] entries of the exhaustive list, [2] grid barrier
+  uint32_t* fb_q1;         // range list: query index of entry i
+  uint32_t* fb_thr1;       // range list: ordered-float threshold of entry i
+  uint32_t* fb_ovf;        // range list: entry i overflowed a candidate buffer in the range pass
+  uint32_t* fb_q2;         // exhaustive list: query indices
+  float* qc_f;             // range list: prepared query rows [entry][ldq] (fp32), their TF32 low parts, bf16 copies
+  float* qc_lo;
+  __nv_bfloat16* qc_h;
+  float errfac_range;      // error factor of the range pass's engine
+  int range_ok;            // 1: unproven queries go to the range list, 0: straight to the exhaustive list
+  int range_keep;          // finalize_range_kernel: most candidates it takes per query (more -> exhaustive list)
 };
 
 // Block-wide radix select: returns the `keep`-th largest of the n distinct keys in s[0..n) (n >= keep >= 1).
@@ -221,6 +241,45 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
   return min(fill, keep);
 }
 
+
+// Rows [0, min(k, ncand)) of the sorted exact keys -> D/I (or packed keys) of query q; the tail is padded.
+__device__ __forceinline__ void write_topk(const FinalizeParams& p, int q, const uint64_t* s2, int ncand) {
+  for (int j = threadIdx.x; j < p.k; j += blockDim.x) {
+    const bool have = j < ncand;
+    uint64_t key = have ? s2[j] : 0ull;
+    if (p.packed) {
+      uint64_t out = 0ull;
+      if (have) out = (key & 0xffffffff00000000ull) | uint64_t(~uint32_t(int64_t(key_id(key)) + p.row_offset));
+      p.packed[int64_t(q) * p.k + j] = out;
+    } else {
+      float sc = p.metric == 0 ? (have ? key_score_max(key) : -FLT_MAX) : (have ? key_score_min(key) : FLT_MAX);
+      p.D[int64_t(q) * p.k + j] = sc;
+      p.I[int64_t(q) * p.k + j] = have ? int64_t(key_id(key)) + p.row_offset : int64_t(-1);
+    }
+  }
+}
+
+// DOT64 re-scoring of candidates s[0..ncand) (approximate keys: only their ids are used) into exact keys s2[j].
+template <typename T>
+__device__ __forceinline__ void rescore_keys(const FinalizeParams& p, const float* qrow, const uint64_t* s, int ncand,
+                                             uint64_t* s2) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const T* X = reinterpret_cast<const T*>(p.X);
+  for (int j = warp; j < ncand; j += nwarp) {
+    uint32_t id = key_id(s[j]);
+    const T* xrow = X + int64_t(id) * p.ld;
+    uint64_t key;
+    if (p.metric == 0) {
+      float out = float(warp_reduce64<Red::kDot>(qrow, xrow, p.d, lane));
+      key = make_key_max(out, id);
+    } else {
+      float out = float(warp_reduce64<Red::kSqDiff>(qrow, xrow, p.d, lane));
+      key = make_key_min(out, id);
+    }
+    if (lane == 0) s2[j] = key;
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -229,8 +288,8 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
   uint64_t* s2 = s + p.sortn;                             // [kp2]
   __shared__ int fill_s;
   __shared__ int off_s[kFinMaxSlots + 1];
-  const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
-  const T* X = reinterpret_cast<const T*>(p.X);
+  __shared__ int handover_s;                              // -1: proven; >= 0: entry in the range list; -2: exhaustive list
+  const int q = blockIdx.x, tid = threadIdx.x;
 
   const uint32_t thrq = p.thr ? p.thr[q] : 0u;
   const int ql = p.interleave ? q % p.qchunk : 0, lq = p.interleave ? q / p.qchunk : 0;
@@ -249,54 +308,110 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
   const float* qrow = p.Q + int64_t(q) * p.ldq;
   for (int j = tid; j < kp2; j += blockDim.x) s2[j] = 0ull;
   __syncthreads();
-  for (int j = warp; j < ncand; j += nwarp) {
-    uint32_t id = key_id(s[j]);
-    const T* xrow = X + int64_t(id) * p.ld;
-    uint64_t key;
-    if (p.metric == 0) {
-      float out = float(warp_reduce64<Red::kDot>(qrow, xrow, p.d, lane));
-      key = make_key_max(out, id);
-    } else {
-      float out = float(warp_reduce64<Red::kSqDiff>(qrow, xrow, p.d, lane));
-      key = make_key_min(out, id);
-    }
-    if (lane == 0) s2[j] = key;
-  }
+  rescore_keys<T>(p, qrow, s, ncand, s2);
   __syncthreads();
   block_bitonic_desc(s2, kp2);
-
-  for (int j = tid; j < p.k; j += blockDim.x) {
-    const bool have = j < ncand;
-    uint64_t key = have ? s2[j] : 0ull;
-    if (p.packed) {
-      uint64_t out = 0ull;
-      if (have) out = (key & 0xffffffff00000000ull) | uint64_t(~uint32_t(int64_t(key_id(key)) + p.row_offset));
-      p.packed[int64_t(q) * p.k + j] = out;
-    } else {
-      float sc = p.metric == 0 ? (have ? key_score_max(key) : -FLT_MAX) : (have ? key_score_min(key) : FLT_MAX);
-      p.D[int64_t(q) * p.k + j] = sc;
-      p.I[int64_t(q) * p.k + j] = have ? int64_t(key_id(key)) + p.row_offset : int64_t(-1);
-    }
-  }
+  write_topk(p, q, s2, ncand);
 
   // completeness proof (thread 0)
-  if (tid == 0 && p.stats) {
-    bool verified = true;
-    if (ncand == p.kp && p.n > p.kp) {           // the list is full, rows may have been filtered out
+  if (tid == 0) {
+    int handover = -1;
+    if (p.stats && ncand == p.kp && p.n > p.kp) {           // the list is full, rows may have been filtered out
       const int kk = p.k < ncand ? p.k : ncand;
-      double amin = double(key_score_max(s[p.kp - 1]));
-      double qn = double(p.qn2[q]), xn = double(*p.maxnorm2);
-      double E = double(p.errfac) * sqrt(qn * xn);
+      const double amin = double(key_score_max(s[p.kp - 1]));
+      const double qn = double(p.qn2[q]), xn = double(*p.maxnorm2);
+      const double nn = sqrt(qn * xn);
+      const double l2x = 2.4e-7 * (xn + qn + nn);            // L2: rounding of the stored norms and of |q|^2
+      bool verified;
+      double thr_range;                                      // every row of the true top-k scores >= thr_range in the range pass
       if (p.metric == 0) {
-        float bound = float(amin + E);                       // any excluded row scores <= bound
-        verified = bound < key_score_max(s2[kk - 1]);
+        const float sk = key_score_max(s2[kk - 1]);
+        verified = float(amin + double(p.errfac) * nn) < sk;                 // any excluded row scores <= that bound
+        thr_range = double(sk) - (double(p.errfac_range) + 1.2e-7) * nn;   // + half an ulp of s_k: keys compare rounded scores
       } else {
-        E += 2.4e-7 * (xn + qn + sqrt(qn * xn));
-        float dlow = float(qn - 2.0 * (amin + E));           // any excluded row is at distance >= dlow
-        verified = dlow > key_score_min(s2[kk - 1]);
+        const float dk = key_score_min(s2[kk - 1]);
+        verified = float(qn - 2.0 * (amin + double(p.errfac) * nn + l2x)) > dk;   // any excluded row is at least that far
+        thr_range = 0.5 * (qn - double(dk)) - (double(p.errfac_range) * nn + 1.5 * l2x);
+      }
+      if (!verified) {
+        atomicAdd(p.stats, 1ull);
+        if (p.fb) {
+          if (p.range_ok) {
+            handover = int(atomicAdd(p.fb + 0, 1u));
+            p.fb_q1[handover] = uint32_t(q);
+            p.fb_thr1[handover] = f32_to_ordered(__double2float_rd(thr_range));
+            p.fb_ovf[handover] = 0u;
+          } else {
+            p.fb_q2[atomicAdd(p.fb + 1, 1u)] = uint32_t(q);
+            atomicAdd(p.stats + 2, 1ull);
+            handover = -2;
+          }
+        } else {
+          atomicAdd(p.stats + 3, 1ull);
+        }
       }
     }
-    if (!verified) atomicAdd(p.stats, 1ull);
+    handover_s = handover;
+  }
+  if (!p.fb || !p.range_ok) return;     // uniform
+  __syncthreads();
+  const int e = handover_s;
+  if (e < 0) return;
+  // the query's prepared row travels to slot e of the compact query buffers the range pass reads through TMA
+  for (int c = tid * 4; c < p.ldq; c += blockDim.x * 4) {
+    const float4 v = ld4(qrow + c);
+    if (p.qc_f) st4(p.qc_f + int64_t(e) * p.ldq + c, v);
+    if (p.qc_h) st4(p.qc_h + int64_t(e) * p.ldq + c, v);
+    if (p.qc_lo) {
+      float4 l;
+      l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+      l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+      l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+      l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+      st4(p.qc_lo + int64_t(e) * p.ldq + c, l);
+    }
+  }
+}
+
+// Second pass of exact mode, per unproven query (entry i of the range list): the range pass left, in the
+// candidate scratch, every row whose approximate score reaches the entry's threshold.  They are all re-scored
+// (DOT64), ordered, and the top-k overwrites the first pass's rows of D/I.  Entries whose candidate set does not
+// fit (a buffer overflowed, or more than range_keep rows) move on to the exhaustive list.  CTAs stride over the
+// entries; the launch is a no-op when the list is empty.
+template <typename T>
+__global__ void __launch_bounds__(kFinThreads) finalize_range_kernel(FinalizeParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* s = reinterpret_cast<uint64_t*>(smem_raw);   // [sortn]
+  uint64_t* s2 = s + p.sortn;                             // [next_pow2(range_keep)]
+  __shared__ int fill_s;
+  __shared__ int off_s[kFinMaxSlots + 1];
+  const int tid = threadIdx.x;
+  const int n1 = int(min(p.fb[0], uint32_t(p.nq)));
+  for (int e = blockIdx.x; e < n1; e += gridDim.x) {
+    const int q = int(p.fb_q1[e]);
+    const int ql = e % p.qchunk, lq = e / p.qchunk;
+    auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
+    auto cnt_of = [&](int slot) -> int { return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per))); };
+    auto key_of = [&](int slot, int i) -> uint64_t { return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)]; };
+    const int got = gather_topk(s, p.sortn, p.range_keep, p.nslots, cnt_of, key_of, 0u, off_s, &fill_s, p.stats + 1, s2);
+    const bool fits = p.fb_ovf[e] == 0u && off_s[p.nslots] <= p.range_keep;   // uniform (shared / global, read after barriers)
+    __syncthreads();
+    if (!fits) {
+      if (tid == 0) {
+        p.fb_q2[atomicAdd(p.fb + 1, 1u)] = uint32_t(q);
+        atomicAdd(p.stats + 2, 1ull);
+      }
+      continue;
+    }
+    int n2p = 2;
+    while (n2p < got) n2p <<= 1;
+    for (int j = tid; j < n2p; j += blockDim.x) s2[j] = 0ull;
+    __syncthreads();
+    rescore_keys<T>(p, p.Q + int64_t(q) * p.ldq, s, got, s2);
+    __syncthreads();
+    block_bitonic_desc(s2, n2p);
+    write_topk(p, q, s2, got);
+    __syncthreads();
   }
 }
 

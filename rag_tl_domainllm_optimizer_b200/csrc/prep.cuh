@@ -144,9 +144,11 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
                                                            __nv_bfloat16* __restrict__ qh, float* __restrict__ qn2,
                                                            float* __restrict__ qlo /* optional: q - trunc_tf32(q) */,
                                                            uint32_t* __restrict__ thr /* [nq] cleared */,
-                                                           unsigned long long* __restrict__ stats /* [2] cleared */) {
-  // the per-search thresholds and counters start at zero: cleared here instead of by two memset launches
-  if (stats && blockIdx.x == 0 && threadIdx.x < 2) stats[threadIdx.x] = 0ull;
+                                                           unsigned long long* __restrict__ stats /* [4] cleared if asked */,
+                                                           uint32_t* __restrict__ fb /* [4] list counters, cleared */) {
+  // the per-search thresholds, counters and hand-over lists start at zero: cleared here instead of by memset launches
+  if (stats && blockIdx.x == 0 && threadIdx.x < 4) stats[threadIdx.x] = 0ull;
+  if (fb && blockIdx.x == 0 && threadIdx.x < 4) fb[threadIdx.x] = 0u;
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;

@@ -30,7 +30,6 @@
 #include <cuda.h>
 #include <algorithm>
 #include <string>
-#include <vector>
 #include "common.cuh"
 #include "finalize.cuh"
 
@@ -67,9 +66,23 @@ struct UmmaParams {
   uint32_t idesc;
   int slot_base;      // first scratch slot of this launch (seed launch: 0, main launch: #seed CTAs)
   int bisect_first;   // seed launch: find the first tile's threshold by bisection over TMEM
+  // range mode (second pass of exact mode): the queries are the entries [q0, q0 + kUmQMax) of the compact list
+  // whose length sits in device memory; thresholds (thr_g, indexed like the list) are FIXED; every score that
+  // reaches its threshold is kept; a buffer that fills up raises the entry's overflow flag instead of compacting
+  int range;
+  const uint32_t* nq_dev;   // range mode: length of the whole list
+  uint32_t* ovf;            // range mode: [list length] overflow flags
+#ifdef B2R_UMMA_PROBE
   float* dbg;         // optional [nq][n] dense scores (probe only)
   int dbg_flags;      // probe only: 1 = load the query tile once per CTA, 2 = skip the MMAs, 4 = skip the filter
+#endif
 };
+
+#ifdef B2R_UMMA_PROBE
+#define B2R_DBG_FLAG(p, bit) ((p).dbg_flags & (bit))
+#else
+#define B2R_DBG_FLAG(p, bit) 0
+#endif
 
 // ---------------------------------------------------------------------------------------------------
 // PTX wrappers
@@ -219,6 +232,14 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // queries of this launch: fixed by the host, or (range mode) this launch's share of the device-side list
+  int nq = p.nq;
+  if (p.range) {
+    const int listed = int(*p.nq_dev);
+    nq = min(max(listed - p.q0, 0), min(p.nq, kUmQMax));
+    if (nq == 0) return;              // uniform over the grid: nothing was left unproven (the normal case)
+  }
+  const int mtiles = (nq + kUmBM - 1) / kUmBM;
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
   const uint32_t tfull0 = smem_u32(bars + 2 * kStages), tempty0 = smem_u32(bars + 2 * kStages + 2);
   const uint32_t split0 = smem_u32(bars + 2 * kStages + 4);   // kSplit: "B_lo written" per stage
@@ -249,7 +270,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   // works on ~gridDim/mtiles neighbouring corpus tiles, so a tile is fetched from HBM once and its re-reads by the
   // other query tiles hit L2 whatever the tile size (a contiguous split would keep gridDim different tiles live
   // at once: 116 MB for fp32 rows of 768, more than L2 holds)
-  const int mitems = p.mtiles;
+  const int mitems = mtiles;
   const int64_t nitems = p.ntiles * mitems;
   const int64_t i0 = blockIdx.x, i1 = nitems, istep = gridDim.x;
   const int kelems = kTf32 ? 32 : 64;   // elements of K per stage
@@ -265,7 +286,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         for (int k = 0; k < p.num_k; ++k) {
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
           const uint32_t sa = stage0 + stage * kStageStride;
-          const bool skip_a = (p.dbg_flags & 1) && (item > i0 || k >= kStages);
+          const bool skip_a = B2R_DBG_FLAG(p, 1) && (item > i0 || k >= kStages);
           mbar_expect_tx(full0 + 8 * stage, kUmBBytes + (skip_a ? 0 : (kSplit ? 2 : 1) * kUmABytes));
           if (!skip_a) {
             tma_load_2d(sa, &tmap_q, full0 + 8 * stage, k * kelems, m * kUmBM);
@@ -291,7 +312,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + kBOff);
 #pragma unroll
           for (int j = 0; j < 4; ++j)   // 4 x 32 bytes of K inside the 128-byte swizzle atom
-            if (!(p.dbg_flags & 2) || (k == 0 && j == 0))
+            if (!B2R_DBG_FLAG(p, 2) || (k == 0 && j == 0))
               tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
           if (kSplit) {
             const uint64_t dalo = make_smem_desc(sa + kAloOff), dblo = make_smem_desc(sa + kBloOff);
@@ -360,8 +381,8 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
       for (int m = m_first; m < m_last; ++m) {
         const int qi = m * kUmBM + tq;
-        const bool valid_q = qi < p.nq;
-        const bool warp_has_q = (m * kUmBM + quarter * 32) < p.nq;
+        const bool valid_q = qi < nq;
+        const bool warp_has_q = (m * kUmBM + quarter * 32) < nq;
         float thr = -INFINITY;
         uint32_t cnt = 0;
         uint32_t* thr_g_q = p.thr_g + p.q0 + (valid_q ? qi : 0);
@@ -374,9 +395,10 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         uint64_t* buf = p.cand + ((size_t(p.slot_base + blockIdx.x) * p.mt_stride + m) * p.cap) * 128 + tq;
         mbar_wait(tfull0 + 8 * acc, acc_phase);
         tc_fence_after();
-        if (g) thr = fmaxf(thr, ordered_to_f32(g));
+        if (p.range) thr = valid_q ? ordered_to_f32(g) : INFINITY;   // fixed threshold of the list entry
+        else if (g) thr = fmaxf(thr, ordered_to_f32(g));
         const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * kUmBN;
-        if (warp_has_q && !(p.dbg_flags & 4)) {
+        if (warp_has_q && !B2R_DBG_FLAG(p, 4)) {
           uint32_t u[32];
           // ---- first tile of this query in this CTA: threshold by bisection over TMEM ----
           if (p.bisect_first && first_visit && ncols >= p.kp) {
@@ -422,7 +444,11 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           for (int c = 0; c < kUmBN / 32; ++c) {
             if (c * 32 >= ncols) break;
             const bool need = valid_q && cnt > uint32_t(p.cap - 32);
-            if (__any_sync(kFull, need)) compact_lanes(buf, cnt, thr, p.kp, p.kmax, thr_g_q, need);
+            if (p.range) {
+              if (need) p.ovf[p.q0 + qi] = 1u;     // too many rows reach the threshold: the exhaustive scan takes over
+            } else if (__any_sync(kFull, need)) {
+              compact_lanes(buf, cnt, thr, p.kp, p.kmax, thr_g_q, need);
+            }
             tmem_ld32(taddr + c * 32, u);
             uint32_t mask = 0u;
 #pragma unroll
@@ -433,7 +459,8 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             }
             const int left = ncols - c * 32;
             if (left < 32) mask &= (1u << left) - 1u;
-            if (!valid_q) mask = 0u;
+            if (!valid_q || (p.range && need)) mask = 0u;
+#ifdef B2R_UMMA_PROBE
             if (p.dbg && valid_q) {   // probe only: dense scores
 #pragma unroll
               for (int i = 0; i < 32; ++i) {
@@ -442,6 +469,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 if (i < left) p.dbg[size_t(qi) * p.n + row + c * 32 + i] = s;
               }
             }
+#endif
             uint32_t any = __reduce_or_sync(kFull, mask);
             if (__popc(any) > 6) {
               // dense chunk (seed tile): walk the statically indexed registers instead of re-reading TMEM
@@ -478,9 +506,9 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
     }
     // counts of this CTA's buffers
-    for (int m = 0; m < p.mtiles; ++m) {
+    for (int m = 0; m < mtiles; ++m) {
       const int qi = m * kUmBM + tq;
-      p.cnt[(size_t(p.slot_base + blockIdx.x) * p.mt_stride + m) * 128 + tq] = qi < p.nq ? cnt_s[qi] : 0u;
+      p.cnt[(size_t(p.slot_base + blockIdx.x) * p.mt_stride + m) * 128 + tq] = qi < nq ? cnt_s[qi] : 0u;
     }
   }
 
@@ -499,31 +527,50 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+constexpr int kUmMaxLaunch = 4;   // query chunks of kUmQMax per call (calls are walked in batches of 8192 queries)
+
+// A tensor map is a pure function of (base, shape, pitch, box): encoded once, reused until any of them changes
+// (the corpus map changes when rows are added or the storage grows, the query maps when a buffer is re-allocated).
+struct TmapSlot {
+  bool valid = false, f32 = false;
+  const void* base = nullptr;
+  uint64_t inner = 0, rows = 0, pitch = 0;
+  uint32_t box_rows = 0;
+  CUtensorMap map;
+};
+
 struct UmmaState {
   PFN_encodeTiled encode = nullptr;
   void* cand = nullptr; size_t cand_bytes = 0;
   void* cnt = nullptr; size_t cnt_bytes = 0;
   bool attr_set[9] = {false, false, false, false, false, false, false, false, false};
+  // slots: 0 corpus (first pass), 1 corpus (range pass), 2.. query maps: [pass][lo][launch]
+  TmapSlot maps[2 + 2 * 2 * kUmMaxLaunch];
   void release() {
     if (cand) cudaFree(cand);
     if (cnt) cudaFree(cnt);
     cand = cnt = nullptr;
     cand_bytes = cnt_bytes = 0;
   }
-  void invalidate() {}
+  void invalidate() { for (TmapSlot& m : maps) m.valid = false; }
 };
 
 struct UmmaCall {
   const void* X; int64_t n; int ld; int d; int storage;
   const void* Qh; const float* Qf; int nq; int kp;
   const float* norm2; uint32_t* thr; int sm_count;
+#ifdef B2R_UMMA_PROBE
   float* dbg = nullptr;
   int dbg_flags = 0;
+#endif
   bool shadow = false;           // X is the bf16 shadow of fp32 rows: operands carry a 2^-9 rounding each
   bool split = false;            // 3xTF32 (fp32 rows): needs Qlo
   const float* Qlo = nullptr;    // q - trunc_tf32(q), same layout as Qf
   cudaEvent_t ev_main0 = nullptr, ev_main1 = nullptr;   // optional: recorded around the main launch(es)
   int64_t main_rows = 0;                                // out: rows the main launch(es) cover
+  // range pass only
+  const uint32_t* list_len = nullptr;   // device: entries in the compact list
+  uint32_t* ovf = nullptr;              // device: [nq] overflow flags
 };
 
 inline bool umma_supported(int storage, int d, int kp, int64_t n) {
@@ -532,23 +579,42 @@ inline bool umma_supported(int storage, int d, int kp, int64_t n) {
   return kp <= 256 && n > 0 && n < (int64_t(1) << 31);
 }
 
-inline int umma_make_map(UmmaState& S, CUtensorMap* map, bool f32, const void* base, uint64_t inner, uint64_t rows,
-                         uint64_t pitch_bytes, uint32_t box_rows, std::string& err) {
-  if (!S.encode) {
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
-    if (e != cudaSuccess || !fn) { err = "cuTensorMapEncodeTiled is not available from this driver"; return -2; }
-    S.encode = reinterpret_cast<PFN_encodeTiled>(fn);
+// Error model of the tensor-core pass, relative to |q||x|: products of bf16 (or truncated-TF32) operands are
+// exact; every tcgen05.mma folds its K-slice (16 bf16 / 8 tf32 products) into the fp32 accumulator, charged
+// here with 2 ulp (2^-23) of the running magnitude per instruction: (d/8 + 8) * 2^-23 for bf16,
+// (d/4 + 8) * 2^-23 for tf32 (measured: 2.8e-7 at d=768, tools/umma_probe, 40x below this).  TF32 adds the
+// truncation of both operands: |trunc(a) trunc(b) - ab| <= (2^-10 + 2^-10 + 2^-20) |ab|.
+// 3xTF32 folds three instructions per K-slice and drops q_lo.x_lo (<= 2^-20) and the TF32 truncation of the two
+// low parts (2 * 2^-21).
+inline float umma_errfac(bool f32, bool split, bool shadow, int d) {
+  return float(split ? (3.0 * double(d) / 4 + 8.0) * 1.1921e-7 + 2.0e-6
+               : f32 ? (double(d) / 4 + 8.0) * 1.1921e-7 + 1.96e-3
+                     : (double(d) / 8 + 8.0) * 1.1921e-7 + (shadow ? 3.92e-3 : 0.0));
+}
+
+inline int umma_get_map(UmmaState& S, int slot, const CUtensorMap** out, bool f32, const void* base, uint64_t inner,
+                        uint64_t rows, uint64_t pitch_bytes, uint32_t box_rows, std::string& err) {
+  TmapSlot& m = S.maps[slot];
+  if (!(m.valid && m.f32 == f32 && m.base == base && m.inner == inner && m.rows == rows && m.pitch == pitch_bytes &&
+        m.box_rows == box_rows)) {
+    if (!S.encode) {
+      void* fn = nullptr;
+      cudaDriverEntryPointQueryResult qres;
+      cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+      if (e != cudaSuccess || !fn) { err = "cuTensorMapEncodeTiled is not available from this driver"; return -2; }
+      S.encode = reinterpret_cast<PFN_encodeTiled>(fn);
+    }
+    cuuint64_t gdim[2] = {inner, rows};
+    cuuint64_t gstride[1] = {pitch_bytes};
+    cuuint32_t box[2] = {f32 ? 32u : 64u, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = S.encode(&m.map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                          const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { m.valid = false; err = "cuTensorMapEncodeTiled failed with code " + std::to_string(int(r)); return -2; }
+    m.valid = true; m.f32 = f32; m.base = base; m.inner = inner; m.rows = rows; m.pitch = pitch_bytes; m.box_rows = box_rows;
   }
-  cuuint64_t gdim[2] = {inner, rows};
-  cuuint64_t gstride[1] = {pitch_bytes};
-  cuuint32_t box[2] = {f32 ? 32u : 64u, box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = S.encode(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                        const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { err = "cuTensorMapEncodeTiled failed with code " + std::to_string(int(r)); return -2; }
+  *out = &m.map;
   return 0;
 }
 
@@ -575,36 +641,47 @@ __global__ void __launch_bounds__(kFinThreads) seed_select_kernel(FinalizeParams
   for (int sl = threadIdx.x; sl < p.nslots; sl += blockDim.x) cnt_w[blk_of(sl) * 128 + (ql & 127)] = sl == 0 ? uint32_t(got) : 0u;
 }
 
-inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
-  const bool f32 = c.storage == 0;
-  const int kelems = f32 ? 32 : 64;
-  const int num_k = (c.d + kelems - 1) / kelems;
-  const int64_t ntiles = (c.n + kUmBN - 1) / kUmBN;
+// Shape of one call's launches and scratch (shared by the first pass and the range pass).
+struct UmmaPlan {
+  bool f32; int esz, kelems, num_k; int64_t ntiles; int tiles_seed; int64_t tiles_main;
+  int grid_seed, grid_main, grid_range, slots, cap, kmax, nlaunch, mt_max;
+};
+
+inline UmmaPlan umma_plan(const UmmaCall& c) {
+  UmmaPlan P{};
+  P.f32 = c.storage == 0;
+  P.esz = P.f32 ? 4 : 2;
+  P.kelems = P.f32 ? 32 : 64;
+  P.num_k = (c.d + P.kelems - 1) / P.kelems;
+  P.ntiles = (c.n + kUmBN - 1) / kUmBN;
   // seed launch: one tile per CTA over the first rows; main launch: everything after them
   // (seed size: enough rows for a sharp threshold, few enough CTAs for a cheap selection)
-  const int64_t seed_want = std::max<int64_t>(32, std::min<int64_t>(c.sm_count, ntiles / 64));
+  const int64_t seed_want = std::max<int64_t>(32, std::min<int64_t>(c.sm_count, P.ntiles / 64));
   const int mt_all = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
   const int seed_cap = mt_all > 1 ? c.sm_count - (c.sm_count - 1) % mt_all : c.sm_count;   // see grid_seed below
   // a corpus of at most one tile per CTA is finished by the seed launch alone (no select, no main launch)
-  const int tiles_seed = ntiles <= seed_cap ? int(ntiles) : int(std::min<int64_t>(seed_want, seed_cap));
-  const int64_t tiles_main = ntiles - tiles_seed;
+  P.tiles_seed = P.ntiles <= seed_cap ? int(P.ntiles) : int(std::min<int64_t>(seed_want, seed_cap));
+  P.tiles_main = P.ntiles - P.tiles_seed;
   // CTAs: the (tile, query tile) items of a launch are spread over up to one CTA per SM
   // seed grid: with round-robin items CTA b visits query tile (b + j*grid) % mt on its j-th item; a grid size that
   // is 1 modulo mt makes consecutive visits hit different query tiles, so every (CTA, query) gets exactly one seed
   // tile and its threshold comes from the in-TMEM bisection (a second visit would flood the buffer)
-  int grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(tiles_seed) * mt_all));
-  if (mt_all > 1 && int64_t(tiles_seed) * mt_all > grid_seed) grid_seed -= (grid_seed - 1) % mt_all;
-  const int grid_main = int(std::min<int64_t>(c.sm_count, tiles_main * mt_all));
-  const int slots = grid_seed + grid_main;
-  int cap = 128;
-  while (cap < 4 * c.kp) cap <<= 1;
-  const int kmax = cap / 2 - 16;
-  const int esz = f32 ? 4 : 2;
+  P.grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(P.tiles_seed) * mt_all));
+  if (mt_all > 1 && int64_t(P.tiles_seed) * mt_all > P.grid_seed) P.grid_seed -= (P.grid_seed - 1) % mt_all;
+  P.grid_main = int(std::min<int64_t>(c.sm_count, P.tiles_main * mt_all));
+  P.grid_range = int(std::min<int64_t>(c.sm_count, P.ntiles));
+  P.slots = std::max(P.grid_seed + P.grid_main, P.grid_range);
+  P.cap = 128;
+  while (P.cap < 4 * c.kp) P.cap <<= 1;
+  P.kmax = P.cap / 2 - 16;
+  P.nlaunch = (c.nq + kUmQMax - 1) / kUmQMax;
+  P.mt_max = mt_all;
+  return P;
+}
 
-  const int nlaunch = (c.nq + kUmQMax - 1) / kUmQMax;
-  const int mt_max = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
-  const size_t cand_need = size_t(nlaunch) * slots * mt_max * cap * 128 * 8;
-  const size_t cnt_need = size_t(nlaunch) * slots * mt_max * 128 * 4;
+inline int umma_scratch(UmmaState& S, const UmmaPlan& P, std::string& err) {
+  const size_t cand_need = size_t(P.nlaunch) * P.slots * P.mt_max * P.cap * 128 * 8;
+  const size_t cnt_need = size_t(P.nlaunch) * P.slots * P.mt_max * 128 * 4;
   if (cand_need > S.cand_bytes) {
     if (S.cand) cudaFree(S.cand);
     S.cand = nullptr; S.cand_bytes = 0;
@@ -617,13 +694,13 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     if (cudaMalloc(&S.cnt, cnt_need) != cudaSuccess) { cudaGetLastError(); err = "counter scratch allocation failed"; return -3; }
     S.cnt_bytes = cnt_need;
   }
+  return 0;
+}
 
-  CUtensorMap tmx;
-  int rc = umma_make_map(S, &tmx, f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * esz, kUmBN, err);
-  if (rc) return rc;
+inline cudaError_t umma_kernel_launch(UmmaState& S, const UmmaCall& c, bool f32, int grid, const CUtensorMap& tmq,
+                                      const CUtensorMap& tmqlo, const CUtensorMap& tmx, const UmmaParams& p, cudaStream_t st) {
   const int variant = (f32 ? 2 : 0) + (c.norm2 ? 1 : 0);
-  auto launch = [&](int grid, const CUtensorMap& tmq, const CUtensorMap& tmqlo, const UmmaParams& p) -> cudaError_t {
-    cudaError_t e = cudaSuccess;
+  cudaError_t e = cudaSuccess;
 #define B2R_UM_LAUNCH(TF, L2, SP)                                                                                  \
   do {                                                                                                             \
     const int vi = variant * 2 + (SP ? 1 : 0);                                                                     \
@@ -634,71 +711,92 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     if (e == cudaSuccess)                                                                                          \
       score_umma_kernel<TF, L2, SP><<<grid, SP ? kUmThreadsSplit : kUmThreads, kUmSmemBytes, st>>>(tmq, tmqlo, tmx, p); \
   } while (0)
-    if (c.split) {   // 3xTF32: fp32 rows only
-      if (c.norm2) B2R_UM_LAUNCH(true, true, true); else B2R_UM_LAUNCH(true, false, true);
-    } else {
-      if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true, false); else B2R_UM_LAUNCH(true, false, false); }
-      else     { if (c.norm2) B2R_UM_LAUNCH(false, true, false); else B2R_UM_LAUNCH(false, false, false); }
-    }
+  if (c.split) {   // 3xTF32: fp32 rows only
+    if (c.norm2) B2R_UM_LAUNCH(true, true, true); else B2R_UM_LAUNCH(true, false, true);
+  } else {
+    if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true, false); else B2R_UM_LAUNCH(true, false, false); }
+    else     { if (c.norm2) B2R_UM_LAUNCH(false, true, false); else B2R_UM_LAUNCH(false, false, false); }
+  }
 #undef B2R_UM_LAUNCH
-    if (e == cudaSuccess) e = cudaGetLastError();
-    return e;
-  };
+  if (e == cudaSuccess) e = cudaGetLastError();
+  return e;
+}
 
-  // layout of the scratch for the merge kernel: slot = CTA of either launch, interleaved [m][entry][128]
+inline uint32_t umma_idesc(bool f32) {
+  return (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
+}
+
+// Query maps of launch l.  Rows are padded to whole 128-query boxes (the buffers are sized for it; rows >= nq only
+// feed ignored outputs): boxes that stay inside the tensor avoid TMA's out-of-bounds handling on every load.
+inline int umma_query_maps(UmmaState& S, const UmmaCall& c, const UmmaPlan& P, int pass, int l, int nq,
+                           const CUtensorMap** tmq, const CUtensorMap** tmqlo, std::string& err) {
+  const int q0 = l * kUmQMax;
+  const char* qbase = P.f32 ? reinterpret_cast<const char*>(c.Qf) : reinterpret_cast<const char*>(c.Qh);
+  const uint64_t nq_box = uint64_t((nq + 2 * kUmBM - 1) / (2 * kUmBM)) * (2 * kUmBM);
+  const int base_slot = 2 + pass * 2 * kUmMaxLaunch;
+  int rc = umma_get_map(S, base_slot + l, tmq, P.f32, qbase + size_t(q0) * c.ld * P.esz, uint64_t(c.ld), nq_box,
+                        uint64_t(c.ld) * P.esz, kUmBM, err);
+  if (rc) return rc;
+  const char* qlo = c.split ? reinterpret_cast<const char*>(c.Qlo) : qbase;   // unused map when not split
+  return umma_get_map(S, base_slot + kUmMaxLaunch + l, tmqlo, P.f32, qlo + size_t(q0) * c.ld * P.esz, uint64_t(c.ld), nq_box,
+                      uint64_t(c.ld) * P.esz, kUmBM, err);
+}
+
+inline void umma_fill_finalize(const UmmaState& S, const UmmaPlan& P, int nslots, int slot_total, FinalizeParams& fp) {
+  // layout of the scratch for the merge kernels: slot = CTA of either launch, interleaved [m][entry][128]
   fp.cand = reinterpret_cast<const uint64_t*>(S.cand);
   fp.cnt = reinterpret_cast<const uint32_t*>(S.cnt);
-  fp.nslots = slots;
-  fp.slot_total = slots;
-  fp.per = cap;
+  fp.nslots = nslots;
+  fp.slot_total = slot_total;
+  fp.per = P.cap;
   fp.interleave = 128;
-  fp.mt_max = mt_max;
+  fp.mt_max = P.mt_max;
   fp.qchunk = kUmQMax;
   fp.slot_stride = 0;
   fp.q_stride = 0;
-  // Error model of the tensor-core pass, relative to |q||x|: products of bf16 (or truncated-TF32) operands are
-  // exact; every tcgen05.mma folds its K-slice (16 bf16 / 8 tf32 products) into the fp32 accumulator, charged
-  // here with 2 ulp (2^-23) of the running magnitude per instruction: (d/8 + 8) * 2^-23 for bf16,
-  // (d/4 + 8) * 2^-23 for tf32 (measured: 2.8e-7 at d=768, tools/umma_probe, 40x below this).  TF32 adds the
-  // truncation of both operands: |trunc(a) trunc(b) - ab| <= (2^-10 + 2^-10 + 2^-20) |ab|.
-  // 3xTF32 folds three instructions per K-slice and drops q_lo.x_lo (<= 2^-20) and the TF32 truncation of the two
-  // low parts (2 * 2^-21).
-  fp.errfac = float(c.split ? (3.0 * double(c.d) / 4 + 8.0) * 1.1921e-7 + 2.0e-6
-                    : f32   ? (double(c.d) / 4 + 8.0) * 1.1921e-7 + 1.96e-3
-                            : (double(c.d) / 8 + 8.0) * 1.1921e-7 + (c.shadow ? 3.92e-3 : 0.0));
+}
 
-  std::vector<CUtensorMap> tmq(nlaunch), tmqlo(nlaunch);
-  std::vector<UmmaParams> pp(nlaunch);
-  for (int l = 0; l < nlaunch; ++l) {
+// First pass: seed launch(es), threshold selection, main launch(es).
+inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
+  if (c.nq > kUmMaxLaunch * kUmQMax) { err = "too many queries for one tcgen05 call"; return -5; }
+  const UmmaPlan P = umma_plan(c);
+  int rc = umma_scratch(S, P, err);
+  if (rc) return rc;
+  const CUtensorMap* tmx = nullptr;
+  rc = umma_get_map(S, 0, &tmx, P.f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * P.esz, kUmBN, err);
+  if (rc) return rc;
+  const int slots = P.grid_seed + P.grid_main;
+  umma_fill_finalize(S, P, slots, slots, fp);
+  fp.errfac = umma_errfac(P.f32, c.split, c.shadow, c.d);
+
+  const CUtensorMap* tmq[kUmMaxLaunch];
+  const CUtensorMap* tmqlo[kUmMaxLaunch];
+  UmmaParams pp[kUmMaxLaunch];
+  for (int l = 0; l < P.nlaunch; ++l) {
     const int q0 = l * kUmQMax;
     const int nq = std::min(kUmQMax, c.nq - q0);
-    const char* qbase = f32 ? reinterpret_cast<const char*>(c.Qf) : reinterpret_cast<const char*>(c.Qh);
-    // rows padded to whole 128-query boxes (the buffers are sized for it; rows >= nq only feed ignored outputs):
-    // boxes that stay inside the tensor avoid TMA's out-of-bounds handling on every load
-    const uint64_t nq_box = uint64_t((nq + 2 * kUmBM - 1) / (2 * kUmBM)) * (2 * kUmBM);
-    rc = umma_make_map(S, &tmq[l], f32, qbase + size_t(q0) * c.ld * esz, uint64_t(c.ld), nq_box, uint64_t(c.ld) * esz, kUmBM, err);
-    if (rc) return rc;
-    const char* qlo = c.split ? reinterpret_cast<const char*>(c.Qlo) : qbase;   // unused map when not split
-    rc = umma_make_map(S, &tmqlo[l], f32, qlo + size_t(q0) * c.ld * esz, uint64_t(c.ld), nq_box, uint64_t(c.ld) * esz, kUmBM, err);
+    rc = umma_query_maps(S, c, P, 0, l, nq, &tmq[l], &tmqlo[l], err);
     if (rc) return rc;
     UmmaParams& p = pp[l];
     p = UmmaParams{};
-    p.n = c.n; p.nq = nq; p.q0 = q0; p.mtiles = (nq + kUmBM - 1) / kUmBM; p.mt_stride = mt_max; p.num_k = num_k;
-    p.kp = c.kp; p.cap = cap; p.kmax = kmax; p.bmax = std::min(cap - 40, std::max(2 * c.kp, c.kp + 56)); p.norm2 = c.norm2; p.thr_g = c.thr;
-    p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * slots * mt_max * cap * 128;
-    p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * slots * mt_max * 128;
-    p.idesc = (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
+    p.n = c.n; p.nq = nq; p.q0 = q0; p.mtiles = (nq + kUmBM - 1) / kUmBM; p.mt_stride = P.mt_max; p.num_k = P.num_k;
+    p.kp = c.kp; p.cap = P.cap; p.kmax = P.kmax; p.bmax = std::min(P.cap - 40, std::max(2 * c.kp, c.kp + 56)); p.norm2 = c.norm2; p.thr_g = c.thr;
+    p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * slots * P.mt_max * P.cap * 128;
+    p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * slots * P.mt_max * 128;
+    p.idesc = umma_idesc(P.f32);
+#ifdef B2R_UMMA_PROBE
     p.dbg = c.dbg; p.dbg_flags = c.dbg_flags;
+#endif
     // seed launch
-    p.row0 = 0; p.ntiles = tiles_seed; p.slot_base = 0; p.bisect_first = 1;
-    cudaError_t e = launch(grid_seed, tmq[l], tmqlo[l], p);
+    p.row0 = 0; p.ntiles = P.tiles_seed; p.slot_base = 0; p.bisect_first = 1;
+    cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_seed, *tmq[l], *tmqlo[l], *tmx, p, st);
     if (e != cudaSuccess) { err = std::string("tcgen05 seed launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
   }
-  if (grid_main > 0) {
+  if (P.grid_main > 0) {
     // thresholds from the seed slots, then the main launch over the remaining rows
     FinalizeParams sp = fp;
-    sp.nslots = grid_seed;
+    sp.nslots = P.grid_seed;
     sp.kp = c.kp;
     sp.sortn = 8192;
     if (!S.attr_set[8]) {
@@ -711,11 +809,11 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     if (e != cudaSuccess) { err = std::string("seed_select launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
     if (c.ev_main0) cudaEventRecord(c.ev_main0, st);
-    c.main_rows = c.n - int64_t(tiles_seed) * kUmBN;
-    for (int l = 0; l < nlaunch; ++l) {
+    c.main_rows = c.n - int64_t(P.tiles_seed) * kUmBN;
+    for (int l = 0; l < P.nlaunch; ++l) {
       UmmaParams& p = pp[l];
-      p.row0 = int64_t(tiles_seed) * kUmBN; p.ntiles = tiles_main; p.slot_base = grid_seed; p.bisect_first = 0;
-      e = launch(grid_main, tmq[l], tmqlo[l], p);
+      p.row0 = int64_t(P.tiles_seed) * kUmBN; p.ntiles = P.tiles_main; p.slot_base = P.grid_seed; p.bisect_first = 0;
+      e = umma_kernel_launch(S, c, P.f32, P.grid_main, *tmq[l], *tmqlo[l], *tmx, p, st);
       if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
       ++*launches;
     }
@@ -723,6 +821,40 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   } else {
     // the seed launch was the whole search
     c.main_rows = 0;
+  }
+  return 0;
+}
+
+// Range pass (second pass of exact mode): one launch per query chunk over ALL rows, with the fixed thresholds of
+// the compact list; `c` describes the compact query buffers and the engine of this pass (fp32 rows: 3xTF32),
+// `first` the first pass's call (its plan sized the scratch this pass reuses).
+inline int umma_launch_range(UmmaState& S, UmmaCall& c, const UmmaCall& first, cudaStream_t st, FinalizeParams& fp,
+                             int* launches, std::string& err) {
+  UmmaPlan P = umma_plan(first);       // same scratch geometry (cap, mt_max, nlaunch, slots) as the first pass
+  const bool f32 = c.storage == 0;
+  P.f32 = f32; P.esz = f32 ? 4 : 2; P.kelems = f32 ? 32 : 64; P.num_k = (c.d + P.kelems - 1) / P.kelems;
+  const CUtensorMap* tmx = nullptr;
+  int rc = umma_get_map(S, 1, &tmx, f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * P.esz, kUmBN, err);
+  if (rc) return rc;
+  umma_fill_finalize(S, P, P.grid_range, P.grid_range, fp);
+  for (int l = 0; l < P.nlaunch; ++l) {
+    const int q0 = l * kUmQMax;
+    const int nq = std::min(kUmQMax, c.nq - q0);
+    const CUtensorMap* tmq = nullptr;
+    const CUtensorMap* tmqlo = nullptr;
+    rc = umma_query_maps(S, c, P, 1, l, nq, &tmq, &tmqlo, err);
+    if (rc) return rc;
+    UmmaParams p{};
+    p.n = c.n; p.nq = nq; p.q0 = q0; p.mtiles = (nq + kUmBM - 1) / kUmBM; p.mt_stride = P.mt_max; p.num_k = P.num_k;
+    p.kp = c.kp; p.cap = P.cap; p.kmax = P.kmax; p.bmax = 0; p.norm2 = c.norm2; p.thr_g = c.thr;
+    p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * P.grid_range * P.mt_max * P.cap * 128;
+    p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * P.grid_range * P.mt_max * 128;
+    p.idesc = umma_idesc(f32);
+    p.row0 = 0; p.ntiles = P.ntiles; p.slot_base = 0; p.bisect_first = 0;
+    p.range = 1; p.nq_dev = c.list_len; p.ovf = c.ovf;
+    cudaError_t e = umma_kernel_launch(S, c, f32, P.grid_range, *tmq, *tmqlo, *tmx, p, st);
+    if (e != cudaSuccess) { err = std::string("tcgen05 range launch failed: ") + cudaGetErrorString(e); return -2; }
+    ++*launches;
   }
   return 0;
 }

@@ -157,18 +157,34 @@ class IndexFlat:
                                                  packed.data_ptr(), stream))
         return packed
 
-    def search_packed_async(self, x, k: int, row_offset: int = 0):
-        """Like ``search_packed`` but without the host-side proof check: returns a CUDA int64 tensor of
-        ``n*k + 1`` entries whose last one is this shard's count of unproven queries (exact mode)."""
-        torch = _torch()
+    # -- row-sharded search through the library's own collective ---------------------------------
+    def comm_init(self, unique_id: bytes, rank: int, world: int, row_offset: int) -> None:
+        """Join the NCCL communicator of a row-sharded corpus (``unique_id`` = rank 0's ``nccl_unique_id()``)."""
+        buf = ctypes.create_string_buffer(bytes(unique_id), 128) if world > 1 else None
+        check(_lib.lib().b2r_index_comm_init(self._h, buf, int(rank), int(world), int(row_offset)))
+
+    def search_sharded(self, x, k: int) -> Tuple[object, object]:
+        """Collective: every rank calls it with the same queries; returns the global top-k on every rank."""
+        k = int(k)
+        if k <= 0:
+            raise ShapeError(f"k must be positive, got {k}")
         kind, obj, ptr, n, stream, dev = _as_f32_2d(x, self.d, "x")
-        device = torch.device("cuda", self.device)
-        if kind != "cuda":
-            stream = torch.cuda.current_stream(device).cuda_stream
-        buf = torch.empty((n * int(k) + 1,), dtype=torch.int64, device=device)
-        check(_lib.lib().b2r_index_search_packed_async(self._h, n, ptr, int(k), int(self.normalize), int(row_offset),
-                                                       buf.data_ptr(), stream))
-        return buf
+        L = _lib.lib()
+        if kind == "cuda":
+            torch = _torch()
+            if dev != self.device:
+                raise ShapeError(f"x is on cuda:{dev}, the index on cuda:{self.device}")
+            D = torch.empty((n, k), dtype=torch.float32, device=obj.device)
+            I = torch.empty((n, k), dtype=torch.int64, device=obj.device)
+            check(L.b2r_index_search_sharded(self._h, n, ptr, k, int(self.normalize), D.data_ptr(), I.data_ptr(), stream))
+            return D, I
+        D = np.empty((n, k), dtype=np.float32)
+        I = np.empty((n, k), dtype=np.int64)
+        check(L.b2r_index_search_sharded(self._h, n, ptr, k, int(self.normalize), D.ctypes.data, I.ctypes.data, 0))
+        if kind == "cpu_torch":
+            torch = _torch()
+            return torch.from_numpy(D), torch.from_numpy(I)
+        return D, I
 
     # -- tuning / introspection ------------------------------------------------------------
     def set_engine(self, engine: int) -> None:
@@ -176,7 +192,7 @@ class IndexFlat:
         self.engine = int(engine)
 
     def set_verify(self, on: bool) -> None:
-        """Exact mode: proof read-back + fallback after each search (default on; off keeps searches asynchronous)."""
+        """Device-side re-search of unproven queries after each search (default on; off only counts them)."""
         check(_lib.lib().b2r_index_set_verify(self._h, int(bool(on))))
 
     def set_pad(self, pad: int) -> None:
@@ -224,8 +240,15 @@ def merge_packed(packed, metric: int = METRIC_INNER_PRODUCT):
     return D, I
 
 
+def nccl_unique_id() -> bytes:
+    """A fresh 128-byte ncclUniqueId (rank 0 calls this and sends it to the other ranks)."""
+    buf = ctypes.create_string_buffer(128)
+    check(_lib.lib().b2r_nccl_unique_id(buf))
+    return buf.raw
+
+
 def merge_packed_strided(gathered, n: int, k: int, metric: int = METRIC_INNER_PRODUCT):
-    """[G, n*k + 1] payloads of ``search_packed_async`` (CUDA int64) -> (D [n,k], I [n,k])."""
+    """[G, >= n*k] payloads whose first n*k words are packed hits (CUDA int64) -> (D [n,k], I [n,k])."""
     torch = _torch()
     if gathered.dim() != 2 or not gathered.is_cuda or gathered.dtype != torch.int64 or gathered.shape[1] < n * k:
         raise ShapeError("gathered must be a CUDA int64 tensor of shape [G, >= n*k]")

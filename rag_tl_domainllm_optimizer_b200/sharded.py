@@ -4,15 +4,19 @@ Rank r owns the contiguous rows ``[r*ceil(N/G), min(N,(r+1)*ceil(N/G)))`` (SURVE
 the shard-local kernels with ``row_offset`` = first owned row, leaves the shard's top-k PACKED (one uint64
 per hit), all-gathers the ``[nq,k]`` payloads with a single collective (NCCL over NVLink on GPUs) and merges
 the ``G*k`` candidates per query with the same comparator — so the result equals the unsharded search.
+
+On GPUs the whole step lives behind the C ABI (``b2r_index_search_sharded``: local search, ``ncclAllGather``
+into a buffer the handle keeps, merge kernel, all enqueued on the caller's stream with no host round trip);
+this class only sets the communicator up (rank 0's ``ncclUniqueId`` travels through ``torch.distributed``).
+The ``torch.distributed`` route below it is the same three steps spelled out in Python: it serves backends
+other than NCCL (the CPU ``gloo`` tests, with the kernels stood in for) and ``native=False``.
 """
 from __future__ import annotations
 
 from typing import Tuple
 
-import numpy as np
-
 from ._lib import METRIC_INNER_PRODUCT
-from .index import IndexFlat, merge_packed, merge_packed_strided
+from .index import IndexFlat, merge_packed, nccl_unique_id
 
 
 def shard_bounds(n: int, world: int, rank: int) -> Tuple[int, int]:
@@ -25,7 +29,7 @@ class ShardedIndexFlat:
     """Every rank constructs it, adds ITS rows (``add_local``) and calls ``search`` with the same queries."""
 
     def __init__(self, d: int, metric: int = METRIC_INNER_PRODUCT, *, storage: str = "f32", device: int | None = None,
-                 normalize: bool = False, shadow: bool = False, group=None, _local=None, _merge=None):
+                 normalize: bool = False, shadow: bool = False, group=None, native: bool = True, _local=None, _merge=None):
         import torch.distributed as dist
         self._dist = dist
         self.group = group
@@ -37,49 +41,46 @@ class ShardedIndexFlat:
         self.d, self.metric_type = d, metric
         self.row_offset = 0
         self.ntotal_global = 0
+        self._want_native = bool(native) and _local is None
+        self._native_ready = False
+        self._gather_buf = None
 
     def add_local(self, x_local, row_offset: int, ntotal_global: int) -> None:
         """Append this rank's rows; ``row_offset`` is the global id of its first row."""
         if self.local.ntotal == 0:
             self.row_offset = int(row_offset)
+            self._native_ready = False
         self.local.add(x_local)
         self.ntotal_global = int(ntotal_global)
 
+    def _setup_native(self) -> bool:
+        """Collective, once: every rank joins the library's own NCCL communicator."""
+        if self._native_ready:
+            return True
+        if not (self._want_native and self.world > 1 and self._dist.get_backend(self.group) == "nccl"):
+            return False
+        box = [nccl_unique_id() if self.rank == 0 else None]
+        src = self._dist.get_global_rank(self.group, 0) if self.group is not None else 0
+        self._dist.broadcast_object_list(box, src=src, group=self.group)
+        self.local.comm_init(box[0], self.rank, self.world, self.row_offset)
+        self._native_ready = True
+        return True
+
     def search(self, x, k: int):
-        import torch
         if self.world == 1 and self.row_offset == 0 and hasattr(self.local, "search"):
             return self.local.search(x, k)                                # one shard: nothing to gather or merge
-        if not hasattr(self.local, "search_packed_async") or len(x) > 8192:
-            return self._search_synchronous(x, k)
-        # Everything is enqueued before the host looks at anything: shard-local search (its count of unproven
-        # queries rides as the last word of the payload), the single all-gather, the merge.
-        n, k = len(x), int(k)
-        buf = self.local.search_packed_async(x, k, self.row_offset)      # [n*k + 1] on this GPU
-        gathered = torch.empty((self.world, n * k + 1), dtype=buf.dtype, device=buf.device)
-        self._dist.all_gather_into_tensor(gathered, buf.view(1, -1), group=self.group)   # the single collective
-        D, I = merge_packed_strided(gathered, n, k, self.metric_type)
-        if self.local.storage == "f32" and int(gathered[:, n * k].max().item()) != 0:
-            # some shard could not prove its top-k (exact mode): every rank saw the same flags, so every rank
-            # repeats the search with the 3xTF32 variant
-            from ._lib import ENGINE_FMA, ENGINE_UMMA3, B2RError
-            previous = getattr(self.local, "engine", 0)
-            try:
-                self.local.set_engine(ENGINE_UMMA3)
-                try:
-                    D, I = self._search_synchronous(x, k)
-                except B2RError:                      # a shape tcgen05 does not take: the FMA engine does
-                    self.local.set_engine(ENGINE_FMA)
-                    D, I = self._search_synchronous(x, k)
-            finally:
-                self.local.set_engine(previous)
-        return D, I
+        if self._setup_native():
+            return self.local.search_sharded(x, k)                        # search + ncclAllGather + merge, in the library
+        return self._search_torch(x, k)
 
-    def _search_synchronous(self, x, k: int):
+    def _search_torch(self, x, k: int):
         import torch
-        packed = self.local.search_packed(x, k, self.row_offset)          # [nq,k] on this GPU
+        packed = self.local.search_packed(x, k, self.row_offset)          # [nq,k] on this rank's device
         if self.world == 1:
             return self._merge(packed.unsqueeze(0), self.metric_type)
-        gathered = torch.empty((self.world,) + tuple(packed.shape), dtype=packed.dtype, device=packed.device)
+        shape = (self.world,) + tuple(packed.shape)
+        if self._gather_buf is None or tuple(self._gather_buf.shape) != shape or self._gather_buf.device != packed.device:
+            self._gather_buf = torch.empty(shape, dtype=packed.dtype, device=packed.device)   # kept across searches
         # the single collective; the flat [G*nq, k] view is the concatenation form every backend accepts
-        self._dist.all_gather_into_tensor(gathered.view(-1, packed.shape[-1]), packed.contiguous(), group=self.group)
-        return self._merge(gathered, self.metric_type)
+        self._dist.all_gather_into_tensor(self._gather_buf.view(-1, packed.shape[-1]), packed.contiguous(), group=self.group)
+        return self._merge(self._gather_buf, self.metric_type)

@@ -62,10 +62,12 @@ def test_config5_shape_batch4096_bf16(oracle):
     assert st["unverified"] == 0 and st["nq"] == 4096
 
 
-def test_unproven_search_falls_back_and_stays_exact(oracle):
-    """60 exact copies of one row: the gap between the k-th and the K'-th candidate is zero, so the 1xTF32 pass
-    cannot prove completeness; the call must repeat with the 3xTF32 split and still return the lowest ids."""
-    x, q = _data(oracle, 30_000, 256, 4, 60)
+def test_unproven_query_is_researched_alone(oracle):
+    """60 exact copies of one row: the gap between the k-th and the K'-th candidate is zero, so the first pass
+    cannot prove query 0.  Only that query goes through the range pass (every row above a fixed bound is
+    re-scored: no gap needed) and the call still returns the lowest ids; the other 1023 queries of the batch
+    are not searched again."""
+    x, q = _data(oracle, 30_000, 256, 1024, 60)
     x[1000:1060] = x[7]
     q[0] = x[7]
     idx = b2r.IndexFlatIP(256)
@@ -74,7 +76,64 @@ def test_unproven_search_falls_back_and_stays_exact(oracle):
     _check(D, I, *oracle.search_ref(x, q, 10, 0, extra=128))
     assert I[0, 0] == 7 and list(I[0, 1:]) == list(range(1000, 1009))
     st = idx.last_stats()
-    assert st["fallback"] == 1 and st["engine"] == b2r.ENGINE_UMMA3
+    assert st["fallback_queries"] == 1 and st["exhaustive_queries"] == 0 and st["unverified"] == 0
+    assert st["fallback"] == 1 and st["engine"] == b2r.ENGINE_UMMA
+    idx.set_verify(False)                       # without the hand-over the query is only counted
+    idx.search(q, 10)
+    st = idx.last_stats()
+    assert st["unverified"] == 1 and st["fallback_queries"] == 0
+
+
+@pytest.mark.parametrize("storage,metric,engine", [("f32", 0, 0), ("f32", 1, 0), ("bf16", 0, 0), ("f32", 0, 1)])
+def test_thousands_of_tied_rows_end_in_the_exhaustive_scan(oracle, storage, metric, engine):
+    """3000 copies of one row around rank k: the range pass cannot hold every row that reaches its bound
+    (buffers of 96 entries per scoring CTA, 2048 rows per query), so the query goes on to the exhaustive DOT64
+    scan, which has no error bound and cannot fail.  The FMA engine (engine=1) has no range pass and hands
+    over directly.  Result: still the lowest ids, bit-identical scores."""
+    x, q = _data(oracle, 40_000, 128, 37, 61)
+    x[5000:8000] = x[3]
+    q[5] = x[3]
+    q[20] = x[3]
+    idx = b2r.IndexFlat(128, metric, storage=storage)
+    idx.set_engine(engine)
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    xo, qo = (oracle.round_bf16(x), oracle.round_bf16(q)) if storage == "bf16" else (x, q)
+    D0, I0 = oracle.search_ref(xo, qo, 10, metric, extra=4000)
+    _check(D, I, D0, I0)
+    assert list(I[5]) == [3] + list(range(5000, 5009)) and list(I[20]) == list(I[5])
+    st = idx.last_stats()
+    assert st["fallback_queries"] == 2 and st["exhaustive_queries"] == 2 and st["unverified"] == 0
+
+
+def test_constant_corpus_and_large_k(oracle):
+    """Every row identical (all scores tie): ids 0..k-1 for every query, through the exhaustive scan; k = 200."""
+    x = np.tile(np.linspace(-1, 1, 96, dtype=np.float32), (5000, 1))
+    q = np.random.default_rng(3).standard_normal((9, 96)).astype(np.float32)
+    for k in (3, 200):
+        idx = b2r.IndexFlatIP(96)
+        idx.add(x)
+        D, I = idx.search(q, k)
+        assert np.array_equal(I, np.tile(np.arange(k), (9, 1)))
+        D0, _ = oracle.search_defined(x[:k], q, k, 0)
+        assert np.array_equal(_bits(D), _bits(D0))
+        st = idx.last_stats()
+        assert st["exhaustive_queries"] == 9 and st["unverified"] == 0
+
+
+def test_fallback_counters_add_up_over_query_batches(oracle):
+    """A call of more than 8192 queries is walked in batches; an unproven query in the second batch is handled
+    there and the counters of the batches add up on the device (no read-back between them)."""
+    x, q = _data(oracle, 9000, 64, 9000, 62)
+    x[100:150] = x[2]
+    q[8500] = x[2]
+    q[17] = x[2]
+    idx = b2r.IndexFlatIP(64)
+    idx.add(x)
+    D, I = idx.search(q, 5)
+    _check(D, I, *oracle.search_ref(x, q, 5, 0, extra=128))
+    st = idx.last_stats()
+    assert st["nq"] == 9000 and st["fallback_queries"] >= 2 and st["unverified"] == 0
 
 
 @pytest.mark.parametrize("metric", [b2r.METRIC_INNER_PRODUCT, b2r.METRIC_L2])
@@ -181,9 +240,10 @@ def test_exact_mode_with_bf16_shadow(oracle, metric):
     _check(D, I, *oracle.search_ref(x, q[1:], 10, metric))
     st = idx.last_stats()
     assert st["engine"] == b2r.ENGINE_SHADOW and st["unverified"] == 0 and st["fallback"] == 0
-    D, I = idx.search(q, 10)                    # with the tie cluster: falls back, still exact
+    D, I = idx.search(q, 10)                    # with the tie cluster: query 0 takes the range pass, still exact
     _check(D, I, *oracle.search_ref(x, q, 10, metric, extra=128))
-    assert idx.last_stats()["fallback"] == 1
+    st = idx.last_stats()
+    assert st["fallback"] == 1 and st["fallback_queries"] == 1 and st["unverified"] == 0
     assert np.array_equal(idx.reconstruct(77), x[77])
     with pytest.raises(b2r.B2RError):
         b2r.IndexFlatIP(64, storage="bf16", shadow=True)
@@ -229,24 +289,25 @@ def test_more_queries_than_one_batch(oracle):
         assert st["nq"] == 20_000 and st["unverified"] == 0
 
 
-def test_async_packed_search_carries_the_proof_flag(oracle):
-    """The sharded path's payload: n*k packed hits + 1 word = the shard's count of unproven queries."""
+def test_packed_shard_search_is_asynchronous_and_exact(oracle):
+    """The sharded path's payload: packed shard-local hits; an unprovable query in one shard is settled on the
+    device before the payload is read (no flag travels, no host check)."""
     import torch
     x, q = _data(oracle, 40_001, 128, 33, 97)
-    D0, I0 = oracle.search_ref(x, q, 10, 0)
+    x[300:340] = x[5]                                   # tie cluster: shard 0's first pass cannot prove query 0
+    q[0] = x[5]
+    D0, I0 = oracle.search_ref(x, q, 10, 0, extra=128)
     for G in (2, 3):
-        bufs = []
+        bufs, fb = [], 0
         for r in range(G):
             lo, hi = b2r.shard_bounds(len(x), G, r)
             sh = b2r.IndexFlatIP(128)
             sh.add(x[lo:hi])
-            bufs.append(sh.search_packed_async(q, 10, lo))
-        gathered = torch.stack(bufs)
-        assert gathered.shape == (G, 33 * 10 + 1) and int(gathered[:, -1].max().item()) == 0
-        D, I = b2r.merge_packed_strided(gathered, 33, 10, 0)
+            bufs.append(sh.search_packed(q, 10, lo))
+            fb += sh.last_stats()["fallback_queries"]
+        D, I = b2r.merge_packed(torch.stack(bufs), 0)
         _check(D.cpu().numpy(), I.cpu().numpy(), D0, I0)
-    x[300:340] = x[5]                                   # tie cluster: shard 0 cannot prove query 0
-    q[0] = x[5]
-    sh = b2r.IndexFlatIP(128)
-    sh.add(x[:20_000])
-    assert int(sh.search_packed_async(q, 10, 0)[-1].item()) >= 1
+        assert fb >= 1
+        padded = torch.stack([torch.cat([b.flatten(), b.new_zeros(3)]) for b in bufs])      # lists 333 words apart
+        D, I = b2r.merge_packed_strided(padded, 33, 10, 0)
+        _check(D.cpu().numpy(), I.cpu().numpy(), D0, I0)
