@@ -728,7 +728,7 @@ def main():
     # ---- the configs north_star puts its scaling target on, at full size --------------------------------
     scale = []
     # default: both, at every N (the driver's 1/2/4/8 scaling run then carries them), unless the run is already long
-    t_run = time.perf_counter() - T_START
+    t_run = max_over_ranks(time.perf_counter() - T_START)      # the same decision on every rank
     which = args.scale_configs if args.scale_configs is not None else ("c5,c3" if t_run < 400 else "")
     for name in [v for v in which.split(",") if v]:
         if name == "c5":      # configs[4]: 100M x 768 bf16, batch 4096, k=10
