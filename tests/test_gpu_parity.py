@@ -157,6 +157,8 @@ def test_reward_cosine_golden_through_the_gpu(oracle, golden_dir):
         np.testing.assert_allclose(mx, g[f"c{ci}_fact"], rtol=0, atol=2e-6)
         _, rel = b2r.cosine_rows(resp, query[:, None, :])
         np.testing.assert_allclose(rel, g[f"c{ci}_rel"], rtol=0, atol=2e-6)
+        _, gts = b2r.cosine_rows(resp, g[f"c{ci}_gt"][:, None, :])     # ground-truth similarity, reference :99-104
+        np.testing.assert_allclose(gts, g[f"c{ci}_gtsim"], rtol=0, atol=2e-6)
         if docs.shape[1]:
             for i in range(resp.shape[0]):                             # same number through IndexFlatIP, k=1
                 idx = b2r.IndexFlatIP(resp.shape[1], normalize=True)
@@ -244,3 +246,51 @@ def test_c_abi_direct_host_pointers(oracle):
     assert L.b2r_index_search(h, 6, q.ctypes.data, 0, D.ctypes.data, I.ctypes.data, None) == -1
     assert b"k must be positive" in L.b2r_last_error()
     L.b2r_index_free(h)
+
+
+def test_retriever_over_a_real_index_emits_the_oracles_passages(oracle):
+    """FlatRetriever over a real IndexFlatIP produces, per query, the list[str] that the reference
+    consumes at :31-34 / :63-71 — the passages of the oracle's top-k ids, in rank order, with -1 padding skipped."""
+    rng = np.random.default_rng(21)
+    n, d, nq, k = 5000, 384, 33, 4
+    x = oracle.normalize(rng.standard_normal((n, d)).astype(np.float32))
+    x[4000:4003] = x[10]                                   # duplicates: the lower id comes first in the passages too
+    q = oracle.normalize(rng.standard_normal((nq, d)).astype(np.float32))
+    q[0] = x[10]
+    passages = [f"passage #{i}: lorem {i * 7919 % 1000}" for i in range(n)]
+    r = b2r.FlatRetriever(b2r.IndexFlatIP(d))
+    r.add(x[:3000], passages[:3000])
+    r.add(x[3000:], passages[3000:])
+    D0, I0 = oracle.search_defined(x, q, k, 0)
+    docs = r.retrieve(q, k)
+    assert docs == [[passages[i] for i in row] for row in I0]
+    assert docs[0][:2] == [passages[10], passages[4000]]
+    scored = r.search_with_scores(q, k)
+    assert [[p for p, _ in row] for row in scored] == docs
+    assert np.array_equal(np.array([[s for _, s in row] for row in scored], dtype=np.float32).view(np.uint32), D0.view(np.uint32))
+    few = b2r.FlatRetriever(b2r.IndexFlatIP(d))            # k > ntotal: the -1 slots yield no passage
+    few.add(x[:2], passages[:2])
+    assert [len(row) for row in few.retrieve(q[:3], 4)] == [2, 2, 2]
+    # the collated batch pairs each query with ITS passages (the zip at reference :292 / :299)
+    batch = b2r.collate_retrieval_batch([{"query": f"q{i}", "retrieved_docs": docs[i]} for i in range(nq)])
+    assert list(zip(batch["query"], batch["retrieved_docs"]))[5] == ("q5", docs[5])
+
+
+def test_raft_sets_over_a_real_index(oracle):
+    """SURVEY §8 f4 (configs[3] shape, reduced): gold + distractor sets built from a real top-k' search equal the
+    sets built from the oracle's ids."""
+    rng = np.random.default_rng(22)
+    n, d, nq, k = 3000, 4096, 16, 4
+    x = oracle.normalize(rng.standard_normal((n, d)).astype(np.float32))
+    gold = rng.integers(0, n, nq)
+    q = oracle.normalize(x[gold] + 0.5 * oracle.normalize(rng.standard_normal((nq, d)).astype(np.float32)))
+    gold[3] = -1                                           # a sample without a gold document
+    passages = [f"doc {i}" for i in range(n)]
+    r = b2r.FlatRetriever(b2r.IndexFlatIP(d, storage="bf16"), passages)
+    r.index.add(x)
+    sets = r.retrieve_raft(q, gold, k, k_prime=8, seed=5)
+    _, I0 = oracle.search_ref(oracle.round_bf16(x), oracle.round_bf16(q), 8, 0)
+    ids0, pos0 = b2r.raft_select(I0, gold, k, 1.0, 5)
+    assert sets == [[passages[j] for j in row if j >= 0] for row in ids0]
+    for i in range(nq):
+        assert len(sets[i]) == k and (gold[i] < 0 or sets[i][pos0[i]] == passages[gold[i]])
