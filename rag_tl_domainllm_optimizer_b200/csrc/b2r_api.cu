@@ -148,6 +148,7 @@ struct b2r_index {
   DevBuf qf, qh, qlo, qn2, thr, cand, cnt, stats, stage_q, stage_d, stage_i, stage_x, misc;
   DevBuf fb;                           // hand-over lists of unproven queries: 16 counters, then 4 arrays of nq words
   DevBuf qc_f, qc_lo, qc_h;            // their prepared rows, compacted, as the range pass reads them
+  DevBuf qc2_f, qc2_lo;                // ... and as the second (3xTF32) range pass reads them
   DevBuf exl;                          // per-CTA top-k lists of the exhaustive scan
   DevBuf shard_local, shard_all;       // sharded search: this rank's packed top-k, and every rank's
   static constexpr int kEvPool = 256;           // scoring-kernel timers: one event pair per recent search
@@ -221,7 +222,7 @@ extern "C" void b2r_index_free(b2r_index* idx) {
   if (idx->maxnorm2) cudaFree(idx->maxnorm2);
   DevBuf* bufs[] = {&idx->qf, &idx->qh, &idx->qlo, &idx->qn2, &idx->thr, &idx->cand, &idx->cnt, &idx->stats,
                     &idx->stage_q, &idx->stage_d, &idx->stage_i, &idx->stage_x, &idx->misc, &idx->fb, &idx->qc_f,
-                    &idx->qc_lo, &idx->qc_h, &idx->exl, &idx->shard_local, &idx->shard_all};
+                    &idx->qc_lo, &idx->qc_h, &idx->qc2_f, &idx->qc2_lo, &idx->exl, &idx->shard_local, &idx->shard_all};
   for (DevBuf* b : bufs) b->release();
   idx->umma.release();
   for (int i = 0; i < b2r_index::kEvPool; ++i) {
@@ -525,9 +526,12 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   }
   const bool f32 = idx->storage == B2R_STORE_F32;
   // unproven queries are handed on (device side) when the proof can fail at all: rows may only be filtered out
-  // when there are more of them than K'
+  // when there are more of them than K'.  Range passes: fp32 rows searched with one TF32 pass (or its bf16 shadow)
+  // get a 1xTF32 range pass (error band 2e-3: cheap, HBM-bound for up to 128 queries) and, for what does not fit,
+  // a 3xTF32 one (band 7e-5); a forced 3xTF32 engine and bf16 rows get one range pass with their own engine.
   const bool chain = idx->verify && idx->ntotal > kp;
   const bool range_ok = chain && use_umma;
+  const bool range2 = range_ok && f32 && !split;
   int launches = 0;
   const int ldq = idx->ld;
   RC_TRY(idx->qf.ensure(size_t(nq + 256) * ldq * 4));
@@ -536,13 +540,17 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   RC_TRY(idx->qn2.ensure(size_t(nq) * 4));
   RC_TRY(idx->thr.ensure(size_t(nq) * 4));
   RC_TRY(idx->stats.ensure(4 * sizeof(unsigned long long)));
-  RC_TRY(idx->fb.ensure(size_t(kFbHeader + 4 * nq) * 4));
+  RC_TRY(idx->fb.ensure(size_t(kFbHeader + 9 * nq) * 4));
   if (range_ok) {
     if (f32) {
       RC_TRY(idx->qc_f.ensure(size_t(nq + 256) * ldq * 4));
-      RC_TRY(idx->qc_lo.ensure(size_t(nq + 256) * ldq * 4));
+      if (split) RC_TRY(idx->qc_lo.ensure(size_t(nq + 256) * ldq * 4));
     } else {
       RC_TRY(idx->qc_h.ensure(size_t(nq + 256) * ldq * 2));
+    }
+    if (range2) {
+      RC_TRY(idx->qc2_f.ensure(size_t(nq + 256) * ldq * 4));
+      RC_TRY(idx->qc2_lo.ensure(size_t(nq + 256) * ldq * 4));
     }
   }
   uint32_t* fb = static_cast<uint32_t*>(idx->fb.p);
@@ -605,17 +613,25 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   fp.maxnorm2 = idx->maxnorm2;
   fp.D = D; fp.I = I; fp.packed = packed;
   fp.stats = static_cast<unsigned long long*>(idx->stats.p);
+  FbList list1{}, list2{};
   if (chain) {
-    fp.fb = fb;
-    fp.fb_q1 = fb + kFbHeader; fp.fb_thr1 = fb + kFbHeader + nq; fp.fb_ovf = fb + kFbHeader + 2 * nq; fp.fb_q2 = fb + kFbHeader + 3 * nq;
-    fp.range_ok = range_ok ? 1 : 0;
+    fp.ex_n = fb + 1; fp.ex_bar = fb + 2; fp.ex_q = fb + kFbHeader + 8 * nq;
     fp.range_keep = kRangeKeep;
     if (range_ok) {
-      // the range pass runs the most accurate tensor-core variant the rows allow: 3xTF32 on fp32 rows, kind::f16 on bf16 rows
-      fp.errfac_range = umma_errfac(f32, f32, false, int(idx->d));
-      fp.qc_f = f32 ? static_cast<float*>(idx->qc_f.p) : nullptr;
-      fp.qc_lo = f32 ? static_cast<float*>(idx->qc_lo.p) : nullptr;
-      fp.qc_h = f32 ? nullptr : static_cast<__nv_bfloat16*>(idx->qc_h.p);
+      list1.n = fb + 0; list1.q = fb + kFbHeader; list1.thr = fb + kFbHeader + nq; list1.thr_next = fb + kFbHeader + 2 * nq;
+      list1.ovf = fb + kFbHeader + 3 * nq;
+      list1.qc_f = f32 ? static_cast<float*>(idx->qc_f.p) : nullptr;
+      list1.qc_lo = (f32 && split) ? static_cast<float*>(idx->qc_lo.p) : nullptr;
+      list1.qc_h = f32 ? nullptr : static_cast<__nv_bfloat16*>(idx->qc_h.p);
+      fp.errfac_range = umma_errfac(f32, split, false, int(idx->d));
+      fp.errfac_range2 = range2 ? umma_errfac(true, true, false, int(idx->d)) : fp.errfac_range;
+      fp.next = list1;
+    }
+    if (range2) {
+      list2.n = fb + 3; list2.q = fb + kFbHeader + 4 * nq; list2.thr = fb + kFbHeader + 5 * nq; list2.thr_next = fb + kFbHeader + 6 * nq;
+      list2.ovf = fb + kFbHeader + 7 * nq;
+      list2.qc_f = static_cast<float*>(idx->qc2_f.p);
+      list2.qc_lo = static_cast<float*>(idx->qc2_lo.p);
     }
   }
   const size_t smem = size_t(fp.sortn + host_next_pow2(kp)) * 8;
@@ -626,18 +642,20 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   ++launches;
 
   if (chain) {
-    if (range_ok) {
+    // one range pass: scoring launch(es) over the list's compact queries, then its merge
+    auto range_pass = [&](const FbList& cur, const FbList& next, bool pass_split, int pass) -> int {
       UmmaCall rc_call{};
       rc_call.X = idx->X; rc_call.n = idx->ntotal; rc_call.ld = idx->ld; rc_call.d = int(idx->d);
       rc_call.storage = idx->storage;
-      rc_call.Qh = idx->qc_h.p; rc_call.Qf = static_cast<const float*>(idx->qc_f.p); rc_call.Qlo = static_cast<const float*>(idx->qc_lo.p);
+      rc_call.Qh = cur.qc_h; rc_call.Qf = cur.qc_f; rc_call.Qlo = cur.qc_lo;
       rc_call.nq = int(nq); rc_call.kp = kp;
-      rc_call.norm2 = uc.norm2; rc_call.thr = fp.fb_thr1; rc_call.sm_count = idx->sm_count;
-      rc_call.split = f32;
-      rc_call.list_len = fb; rc_call.ovf = fp.fb_ovf;
+      rc_call.norm2 = uc.norm2; rc_call.thr = cur.thr; rc_call.sm_count = idx->sm_count;
+      rc_call.split = pass_split;
+      rc_call.list_len = cur.n; rc_call.ovf = cur.ovf;
       FinalizeParams rp = fp;
+      rp.cur = cur; rp.next = next;
       std::string err;
-      int rc = umma_launch_range(idx->umma, rc_call, uc, st, rp, &launches, err);
+      int rc = umma_launch_range(idx->umma, rc_call, uc, pass, st, rp, &launches, err);
       if (rc != B2R_OK) return fail(rc, "%s", err.c_str());
       rp.sortn = 2 * kRangeKeep;
       const size_t rsmem = size_t(rp.sortn + kRangeKeep) * 8;
@@ -647,7 +665,10 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
       else finalize_range_kernel<__nv_bfloat16><<<rgrid, kFinThreads, rsmem, st>>>(rp);
       CU_TRY(cudaGetLastError());
       ++launches;
-    }
+      return B2R_OK;
+    };
+    if (range_ok) RC_TRY(range_pass(list1, range2 ? list2 : FbList{}, split, 1));
+    if (range2) RC_TRY(range_pass(list2, FbList{}, true, 2));
     // exhaustive DOT64 scan of whatever is still unproven (cooperative: its CTAs meet at a grid barrier)
     FinalizeParams xp = fp;
     xp.sortn = std::max(4096, host_next_pow2(int(k) + 2048));

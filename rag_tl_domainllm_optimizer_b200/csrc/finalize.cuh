@@ -29,6 +29,20 @@ namespace b2r {
 constexpr int kFinThreads = 1024;
 constexpr int kFinMaxSlots = 1024;
 
+// A device-side list of queries handed on to a later pass: entry i = (query index, fixed threshold of the pass that
+// reads the list, threshold for the pass after that, overflow flag) plus the query's prepared row in compact
+// buffers that the pass reads through TMA.  n == nullptr: no such list.
+struct FbList {
+  uint32_t* n;         // entries so far (cleared by prep_queries_kernel)
+  uint32_t* q;
+  uint32_t* thr;       // ordered-float threshold for the pass that reads this list
+  uint32_t* thr_next;  // ... and for the pass after it (a tighter engine), carried along
+  uint32_t* ovf;
+  float* qc_f;         // [entry][ldq] prepared rows (fp32), their TF32 low parts, bf16 copies (whichever the pass needs)
+  float* qc_lo;
+  __nv_bfloat16* qc_h;
+};
+
 struct FinalizeParams {
   const uint64_t* cand;    // candidate keys
   int64_t slot_stride;     // elements between consecutive slots
@@ -49,17 +63,14 @@ struct FinalizeParams {
   float* D; int64_t* I; uint64_t* packed;
   unsigned long long* stats;  // [0] queries unproven by the first pass, [1] candidates seen,
                               // [2] queries sent on to the exhaustive scan, [3] queries left unproven
-  // hand-over of unproven queries (all optional: fb == nullptr keeps the counters only)
-  uint32_t* fb;            // [0] entries of the range list, [1] entries of the exhaustive list, [2] grid barrier
-  uint32_t* fb_q1;         // range list: query index of entry i
-  uint32_t* fb_thr1;       // range list: ordered-float threshold of entry i
-  uint32_t* fb_ovf;        // range list: entry i overflowed a candidate buffer in the range pass
-  uint32_t* fb_q2;         // exhaustive list: query indices
-  float* qc_f;             // range list: prepared query rows [entry][ldq] (fp32), their TF32 low parts, bf16 copies
-  float* qc_lo;
-  __nv_bfloat16* qc_h;
-  float errfac_range;      // error factor of the range pass's engine
-  int range_ok;            // 1: unproven queries go to the range list, 0: straight to the exhaustive list
+  // hand-over of unproven queries: finalize_kernel appends to `next`; finalize_range_kernel reads
+  // `cur` and appends what does not fit to `next`; whoever has no `next` appends to the exhaustive list
+  FbList cur, next;
+  uint32_t* ex_n;          // exhaustive list: entries, query indices, grid barrier word (nullptr: count in stats[3] only)
+  uint32_t* ex_q;
+  uint32_t* ex_bar;
+  float errfac_range;      // error factor of the engine that reads `next`, and of the one after it
+  float errfac_range2;
   int range_keep;          // finalize_range_kernel: most candidates it takes per query (more -> exhaustive list)
 };
 
@@ -242,6 +253,23 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
 }
 
 
+// The prepared row of a handed-on query travels to slot e of the list's compact buffers (block-collective).
+__device__ __forceinline__ void copy_query_row(const FbList& L, int e, const float* qrow, int ldq) {
+  for (int c = threadIdx.x * 4; c < ldq; c += blockDim.x * 4) {
+    const float4 v = ld4(qrow + c);
+    if (L.qc_f) st4(L.qc_f + int64_t(e) * ldq + c, v);
+    if (L.qc_h) st4(L.qc_h + int64_t(e) * ldq + c, v);
+    if (L.qc_lo) {
+      float4 l;
+      l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+      l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+      l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+      l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+      st4(L.qc_lo + int64_t(e) * ldq + c, l);
+    }
+  }
+}
+
 // Rows [0, min(k, ncand)) of the sorted exact keys -> D/I (or packed keys) of query q; the tail is padded.
 __device__ __forceinline__ void write_topk(const FinalizeParams& p, int q, const uint64_t* s2, int ncand) {
   for (int j = threadIdx.x; j < p.k; j += blockDim.x) {
@@ -323,29 +351,29 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
       const double nn = sqrt(qn * xn);
       const double l2x = 2.4e-7 * (xn + qn + nn);            // L2: rounding of the stored norms and of |q|^2
       bool verified;
-      double thr_range;                                      // every row of the true top-k scores >= thr_range in the range pass
+      double base, e_fix;     // a row of the true top-k scores >= base - (errfac * nn + e_fix) in a pass with error factor errfac
       if (p.metric == 0) {
         const float sk = key_score_max(s2[kk - 1]);
         verified = float(amin + double(p.errfac) * nn) < sk;                 // any excluded row scores <= that bound
-        thr_range = double(sk) - (double(p.errfac_range) + 1.2e-7) * nn;   // + half an ulp of s_k: keys compare rounded scores
+        base = double(sk);
+        e_fix = 1.2e-7 * nn;                                                 // half an ulp of s_k: keys compare rounded scores
       } else {
         const float dk = key_score_min(s2[kk - 1]);
         verified = float(qn - 2.0 * (amin + double(p.errfac) * nn + l2x)) > dk;   // any excluded row is at least that far
-        thr_range = 0.5 * (qn - double(dk)) - (double(p.errfac_range) * nn + 1.5 * l2x);
+        base = 0.5 * (qn - double(dk));
+        e_fix = 1.5 * l2x;
       }
       if (!verified) {
         atomicAdd(p.stats, 1ull);
-        if (p.fb) {
-          if (p.range_ok) {
-            handover = int(atomicAdd(p.fb + 0, 1u));
-            p.fb_q1[handover] = uint32_t(q);
-            p.fb_thr1[handover] = f32_to_ordered(__double2float_rd(thr_range));
-            p.fb_ovf[handover] = 0u;
-          } else {
-            p.fb_q2[atomicAdd(p.fb + 1, 1u)] = uint32_t(q);
-            atomicAdd(p.stats + 2, 1ull);
-            handover = -2;
-          }
+        if (p.next.n) {
+          handover = int(atomicAdd(p.next.n, 1u));
+          p.next.q[handover] = uint32_t(q);
+          p.next.thr[handover] = f32_to_ordered(__double2float_rd(base - (double(p.errfac_range) * nn + e_fix)));
+          p.next.thr_next[handover] = f32_to_ordered(__double2float_rd(base - (double(p.errfac_range2) * nn + e_fix)));
+          p.next.ovf[handover] = 0u;
+        } else if (p.ex_n) {
+          p.ex_q[atomicAdd(p.ex_n, 1u)] = uint32_t(q);
+          atomicAdd(p.stats + 2, 1ull);
         } else {
           atomicAdd(p.stats + 3, 1ull);
         }
@@ -353,31 +381,19 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
     }
     handover_s = handover;
   }
-  if (!p.fb || !p.range_ok) return;     // uniform
+  if (!p.next.n) return;     // uniform
   __syncthreads();
   const int e = handover_s;
   if (e < 0) return;
-  // the query's prepared row travels to slot e of the compact query buffers the range pass reads through TMA
-  for (int c = tid * 4; c < p.ldq; c += blockDim.x * 4) {
-    const float4 v = ld4(qrow + c);
-    if (p.qc_f) st4(p.qc_f + int64_t(e) * p.ldq + c, v);
-    if (p.qc_h) st4(p.qc_h + int64_t(e) * p.ldq + c, v);
-    if (p.qc_lo) {
-      float4 l;
-      l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
-      l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
-      l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
-      l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
-      st4(p.qc_lo + int64_t(e) * p.ldq + c, l);
-    }
-  }
+  copy_query_row(p.next, e, qrow, p.ldq);
 }
 
 // Second pass of exact mode, per unproven query (entry i of the range list): the range pass left, in the
 // candidate scratch, every row whose approximate score reaches the entry's threshold.  They are all re-scored
 // (DOT64), ordered, and the top-k overwrites the first pass's rows of D/I.  Entries whose candidate set does not
-// fit (a buffer overflowed, or more than range_keep rows) move on to the exhaustive list.  CTAs stride over the
-// entries; the launch is a no-op when the list is empty.
+// fit (a buffer overflowed, or more than range_keep rows) move on to the next list (a pass with a tighter error
+// bound) or, when there is none, to the exhaustive list.  CTAs stride over the entries; the launch is a no-op when
+// the list is empty.
 template <typename T>
 __global__ void __launch_bounds__(kFinThreads) finalize_range_kernel(FinalizeParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -386,20 +402,36 @@ __global__ void __launch_bounds__(kFinThreads) finalize_range_kernel(FinalizePar
   __shared__ int fill_s;
   __shared__ int off_s[kFinMaxSlots + 1];
   const int tid = threadIdx.x;
-  const int n1 = int(min(p.fb[0], uint32_t(p.nq)));
+  __shared__ int next_s;
+  const int n1 = int(min(*p.cur.n, uint32_t(p.nq)));
   for (int e = blockIdx.x; e < n1; e += gridDim.x) {
-    const int q = int(p.fb_q1[e]);
+    const int q = int(p.cur.q[e]);
     const int ql = e % p.qchunk, lq = e / p.qchunk;
     auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
     auto cnt_of = [&](int slot) -> int { return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per))); };
     auto key_of = [&](int slot, int i) -> uint64_t { return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)]; };
     const int got = gather_topk(s, p.sortn, p.range_keep, p.nslots, cnt_of, key_of, 0u, off_s, &fill_s, p.stats + 1, s2);
-    const bool fits = p.fb_ovf[e] == 0u && off_s[p.nslots] <= p.range_keep;   // uniform (shared / global, read after barriers)
+    const bool fits = p.cur.ovf[e] == 0u && off_s[p.nslots] <= p.range_keep;   // uniform (shared / global, read after barriers)
     __syncthreads();
     if (!fits) {
+      // too many rows reach this pass's bound: on to the pass with the tighter bound, or to the exhaustive scan
       if (tid == 0) {
-        p.fb_q2[atomicAdd(p.fb + 1, 1u)] = uint32_t(q);
-        atomicAdd(p.stats + 2, 1ull);
+        if (p.next.n) {
+          const int e2 = int(atomicAdd(p.next.n, 1u));
+          p.next.q[e2] = uint32_t(q);
+          p.next.thr[e2] = p.cur.thr_next[e];
+          p.next.thr_next[e2] = 0u;
+          p.next.ovf[e2] = 0u;
+          next_s = e2;
+        } else {
+          p.ex_q[atomicAdd(p.ex_n, 1u)] = uint32_t(q);
+          atomicAdd(p.stats + 2, 1ull);
+        }
+      }
+      if (p.next.n) {
+        __syncthreads();
+        copy_query_row(p.next, next_s, p.Q + int64_t(q) * p.ldq, p.ldq);
+        __syncthreads();
       }
       continue;
     }

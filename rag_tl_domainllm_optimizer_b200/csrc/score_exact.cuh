@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(kExThreads) score_exact_kernel(FinalizeParams 
   __shared__ unsigned long long thr_s[kExQB];
   __shared__ int fill_s;
   __shared__ int off_s[kFinMaxSlots + 1];
-  const int n2 = int(min(p.fb[1], uint32_t(p.nq)));
+  const int n2 = int(min(*p.ex_n, uint32_t(p.nq)));
   if (n2 == 0) return;                                      // nothing left unproven: the normal case
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int grid = gridDim.x;
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kExThreads) score_exact_kernel(FinalizeParams 
       if (tid < kExQB) { cnt_s[tid] = 0; thr_s[tid] = 0ull; }
       const float* qrow[kExQB];
 #pragma unroll
-      for (int j = 0; j < kExQB; ++j) qrow[j] = p.Q + int64_t(p.fb_q2[w0 + g0 + (j < nqb ? j : 0)]) * p.ldq;
+      for (int j = 0; j < kExQB; ++j) qrow[j] = p.Q + int64_t(p.ex_q[w0 + g0 + (j < nqb ? j : 0)]) * p.ldq;
       __syncthreads();
       for (int64_t it = 0; it < iters; ++it) {
         const int64_t r = (it * grid + blockIdx.x) * 8 + warp;
@@ -137,17 +137,17 @@ __global__ void __launch_bounds__(kExThreads) score_exact_kernel(FinalizeParams 
       }
       __syncthreads();
     }
-    grid_barrier(p.fb + 2, epoch);
+    grid_barrier(p.ex_bar, epoch);
     // ---------------- phase B: merge the per-CTA lists ----------------
     for (int e = blockIdx.x; e < nw; e += grid) {
-      const int q = int(p.fb_q2[w0 + e]);
+      const int q = int(p.ex_q[w0 + e]);
       auto cnt_of = [&](int) -> int { return p.k; };
       auto key_of = [&](int slot, int i) -> uint64_t { return lists[(size_t(e) * grid + slot) * p.k + i]; };
       const int got = gather_topk(buf, p.sortn, p.k, grid, cnt_of, key_of, 0u, off_s, &fill_s, nullptr, buf + p.sortn);
       write_topk(p, q, buf, got);
       __syncthreads();
     }
-    grid_barrier(p.fb + 2, epoch);
+    grid_barrier(p.ex_bar, epoch);
   }
 }
 

@@ -28,6 +28,7 @@
 // Algorithmic flops: 2 * nq * rows * d.
 #pragma once
 #include <cuda.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <string>
 #include "common.cuh"
@@ -72,6 +73,13 @@ struct UmmaParams {
   int range;
   const uint32_t* nq_dev;   // range mode: length of the whole list
   uint32_t* ovf;            // range mode: [list length] overflow flags
+  // sampling launch (large corpora): the launch's `ntiles` tiles are spread evenly over all `all_tiles` tiles of the
+  // shard; the epilogue keeps no candidate, only the `seed_j` best scores of every (tile, query), from which
+  // seed_thr_kernel derives each query's starting threshold.  The main launch then covers every row.
+  int seed_topj;
+  int seed_j;               // 4 or 8
+  int64_t all_tiles;
+  float* seedv;             // [call nq][ntiles][seed_j]
 #ifdef B2R_UMMA_PROBE
   float* dbg;         // optional [nq][n] dense scores (probe only)
   int dbg_flags;      // probe only: 1 = load the query tile once per CTA, 2 = skip the MMAs, 4 = skip the filter
@@ -164,6 +172,40 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
   d |= uint64_t(1) << 46;
   d |= uint64_t(2) << 61;
   return d;
+}
+
+// running top-J of a stream of scores, kept sorted (descending) in registers, branch-free
+template <int J>
+__device__ __forceinline__ void topj_insert(float (&v)[J], float s) {
+  v[J - 1] = fmaxf(v[J - 1], s);
+#pragma unroll
+  for (int i = J - 1; i > 0; --i) {
+    const float hi = fmaxf(v[i - 1], v[i]), lo = fminf(v[i - 1], v[i]);
+    v[i - 1] = hi;
+    v[i] = lo;
+  }
+}
+
+template <int J, bool kL2>
+__device__ __forceinline__ void seed_topj_tile(uint32_t taddr, int ncols, const float* hn_s, float* out) {
+  float v[J];
+#pragma unroll
+  for (int i = 0; i < J; ++i) v[i] = -INFINITY;
+  uint32_t u[32];
+  for (int c = 0; c < kUmBN / 32; ++c) {
+    if (c * 32 >= ncols) break;
+    tmem_ld32(taddr + c * 32, u);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      float s = __uint_as_float(u[i]);
+      if (kL2) s -= hn_s[c * 32 + i];
+      topj_insert<J>(v, c * 32 + i < ncols ? s : -INFINITY);
+    }
+  }
+  if (out) {
+#pragma unroll
+    for (int i = 0; i < J; i += 4) *reinterpret_cast<float4*>(out + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -282,7 +324,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       for (int64_t item = i0; item < i1; item += istep) {
         const int64_t t = item / mitems;
         const int m = int(item - t * mitems);
-        const int row = int(p.row0 + t * kUmBN);
+        const int row = int(p.row0 + (p.seed_topj ? (t * p.all_tiles) / p.ntiles : t) * kUmBN);
         for (int k = 0; k < p.num_k; ++k) {
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
           const uint32_t sa = stage0 + stage * kStageStride;
@@ -371,7 +413,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       const int m_last = mg + 1;
       const bool first_visit = !((seen_m >> mg) & 1u);   // first time this CTA sees these query tiles
       seen_m |= 1u << mg;
-      const int64_t row = p.row0 + t * kUmBN;
+      const int64_t row = p.row0 + (p.seed_topj ? (t * p.all_tiles) / p.ntiles : t) * kUmBN;
       const int ncols = int(p.n - row < kUmBN ? p.n - row : kUmBN);
       if (kL2 && t != t_prev) {
         t_prev = t;
@@ -398,7 +440,13 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         if (p.range) thr = valid_q ? ordered_to_f32(g) : INFINITY;   // fixed threshold of the list entry
         else if (g) thr = fmaxf(thr, ordered_to_f32(g));
         const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * kUmBN;
-        if (warp_has_q && !B2R_DBG_FLAG(p, 4)) {
+        if (p.seed_topj) {
+          if (warp_has_q) {
+            float* out = valid_q ? p.seedv + (size_t(p.q0 + qi) * p.ntiles + t) * p.seed_j : nullptr;
+            if (p.seed_j == 4) seed_topj_tile<4, kL2>(taddr, ncols, hn_s, out);
+            else seed_topj_tile<8, kL2>(taddr, ncols, hn_s, out);
+          }
+        } else if (warp_has_q && !B2R_DBG_FLAG(p, 4)) {
           uint32_t u[32];
           // ---- first tile of this query in this CTA: threshold by bisection over TMEM ----
           if (p.bisect_first && first_visit && ncols >= p.kp) {
@@ -506,7 +554,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
     }
     // counts of this CTA's buffers
-    for (int m = 0; m < mtiles; ++m) {
+    for (int m = 0; m < (p.seed_topj ? 0 : mtiles); ++m) {
       const int qi = m * kUmBM + tq;
       p.cnt[(size_t(p.slot_base + blockIdx.x) * p.mt_stride + m) * 128 + tq] = qi < nq ? cnt_s[qi] : 0u;
     }
@@ -543,14 +591,16 @@ struct UmmaState {
   PFN_encodeTiled encode = nullptr;
   void* cand = nullptr; size_t cand_bytes = 0;
   void* cnt = nullptr; size_t cnt_bytes = 0;
+  void* seedv = nullptr; size_t seedv_bytes = 0;
   bool attr_set[9] = {false, false, false, false, false, false, false, false, false};
   // slots: 0 corpus (first pass), 1 corpus (range pass), 2.. query maps: [pass][lo][launch]
-  TmapSlot maps[2 + 2 * 2 * kUmMaxLaunch];
+  TmapSlot maps[2 + 3 * 2 * kUmMaxLaunch];
   void release() {
     if (cand) cudaFree(cand);
     if (cnt) cudaFree(cnt);
-    cand = cnt = nullptr;
-    cand_bytes = cnt_bytes = 0;
+    if (seedv) cudaFree(seedv);
+    cand = cnt = seedv = nullptr;
+    cand_bytes = cnt_bytes = seedv_bytes = 0;
   }
   void invalidate() { for (TmapSlot& m : maps) m.valid = false; }
 };
@@ -618,34 +668,45 @@ inline int umma_get_map(UmmaState& S, int slot, const CUtensorMap** out, bool f3
   return 0;
 }
 
-// Seed thresholds: K'-th best candidate of the seed launch's slots -> thr_g[q] (a valid lower bound of the final
-// K'-th best, since it is the K'-th best score of a real subset of the rows).  One CTA per query.
-__global__ void __launch_bounds__(kFinThreads) seed_select_kernel(FinalizeParams p, uint32_t* thr_g) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  uint64_t* s = reinterpret_cast<uint64_t*>(smem_raw);
-  __shared__ int fill_s;
-  __shared__ int off_s[kFinMaxSlots + 1];
-  const int q = blockIdx.x;
-  const int ql = q % p.qchunk, lq = q / p.qchunk;
-  auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
-  auto cnt_of = [&](int slot) -> int { return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per))); };
-  auto key_of = [&](int slot, int i) -> uint64_t { return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)]; };
-  const int got = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, 0u, off_s, &fill_s, nullptr, s + p.sortn);
-  if (threadIdx.x == 0 && got == p.kp) atomicMax(thr_g + q, uint32_t(s[p.kp - 1] >> 32));
-  // Leave only the survivors behind: the best K' of the seed rows go to seed slot 0, the other seed slots of
-  // this query are emptied, so the final merge gathers K' seed entries instead of every seed CTA's list.
-  uint64_t* cand_w = const_cast<uint64_t*>(p.cand);
-  uint32_t* cnt_w = const_cast<uint32_t*>(p.cnt);
-  __syncthreads();
-  for (int i = threadIdx.x; i < got; i += blockDim.x) cand_w[(blk_of(0) * p.per + i) * 128 + (ql & 127)] = s[i];
-  for (int sl = threadIdx.x; sl < p.nslots; sl += blockDim.x) cnt_w[blk_of(sl) * 128 + (ql & 127)] = sl == 0 ? uint32_t(got) : 0u;
+// Starting thresholds from the sampling launch: thr_g[q] = the K'-th largest of the nvals sampled scores of query q
+// (the `seed_j` best of each sampled tile).  Every one of them is the score of a real row, computed exactly as
+// the main launch will compute it, so at least K' rows reach it: a valid lower bound of the final K'-th best.
+// One warp per query; radix select, one bit per step, over the order-preserving uint image of the scores.
+constexpr int kSeedThrWarps = 8;
+__global__ void __launch_bounds__(kSeedThrWarps * 32) seed_thr_kernel(const float* __restrict__ seedv, int nq, int nvals,
+                                                                       int kp, uint32_t* __restrict__ thr_g) {
+  extern __shared__ uint32_t sk_all[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * kSeedThrWarps + warp;
+  if (q >= nq) return;
+  uint32_t* sk = sk_all + size_t(warp) * nvals;
+  const float* v = seedv + size_t(q) * nvals;
+  for (int i = lane; i < nvals; i += 32) sk[i] = f32_to_ordered(v[i]);
+  __syncwarp();
+  uint32_t prefix = 0u;
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t cand = prefix | (1u << bit);
+    int c = 0;
+    for (int i = lane; i < nvals; i += 32) c += sk[i] >= cand ? 1 : 0;
+    c = __reduce_add_sync(kFull, c);
+    if (c >= kp) prefix = cand;
+  }
+  if (lane == 0) thr_g[q] = prefix;     // 0 ("none yet") when fewer than K' values were sampled
 }
 
 // Shape of one call's launches and scratch (shared by the first pass and the range pass).
 struct UmmaPlan {
-  bool f32; int esz, kelems, num_k; int64_t ntiles; int tiles_seed; int64_t tiles_main;
+  bool f32; int esz, kelems, num_k; int64_t ntiles;
+  bool single;           // small corpus: ONE launch (one tile per CTA and query tile, threshold by in-TMEM bisection)
+  int tiles_seed;        // sampled tiles of the sampling launch (large corpora)
+  int seed_j;
   int grid_seed, grid_main, grid_range, slots, cap, kmax, nlaunch, mt_max;
 };
+
+inline int umma_env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
 
 inline UmmaPlan umma_plan(const UmmaCall& c) {
   UmmaPlan P{};
@@ -654,23 +715,28 @@ inline UmmaPlan umma_plan(const UmmaCall& c) {
   P.kelems = P.f32 ? 32 : 64;
   P.num_k = (c.d + P.kelems - 1) / P.kelems;
   P.ntiles = (c.n + kUmBN - 1) / kUmBN;
-  // seed launch: one tile per CTA over the first rows; main launch: everything after them
-  // (seed size: enough rows for a sharp threshold, few enough CTAs for a cheap selection)
-  const int64_t seed_want = std::max<int64_t>(32, std::min<int64_t>(c.sm_count, P.ntiles / 64));
   const int mt_all = (std::min(c.nq, kUmQMax) + kUmBM - 1) / kUmBM;
-  const int seed_cap = mt_all > 1 ? c.sm_count - (c.sm_count - 1) % mt_all : c.sm_count;   // see grid_seed below
-  // a corpus of at most one tile per CTA is finished by the seed launch alone (no select, no main launch)
-  P.tiles_seed = P.ntiles <= seed_cap ? int(P.ntiles) : int(std::min<int64_t>(seed_want, seed_cap));
-  P.tiles_main = P.ntiles - P.tiles_seed;
-  // CTAs: the (tile, query tile) items of a launch are spread over up to one CTA per SM
-  // seed grid: with round-robin items CTA b visits query tile (b + j*grid) % mt on its j-th item; a grid size that
-  // is 1 modulo mt makes consecutive visits hit different query tiles, so every (CTA, query) gets exactly one seed
-  // tile and its threshold comes from the in-TMEM bisection (a second visit would flood the buffer)
-  P.grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(P.tiles_seed) * mt_all));
-  if (mt_all > 1 && int64_t(P.tiles_seed) * mt_all > P.grid_seed) P.grid_seed -= (P.grid_seed - 1) % mt_all;
-  P.grid_main = int(std::min<int64_t>(c.sm_count, P.tiles_main * mt_all));
+  // Small corpus (at most one tile per CTA): a single launch.  With round-robin items CTA b visits query tile
+  // (b + j*grid) % mt on its j-th item; a grid size that is 1 modulo mt makes consecutive visits hit different
+  // query tiles, so every (CTA, query) gets exactly one tile and its threshold comes from the in-TMEM bisection.
+  const int single_cap = mt_all > 1 ? c.sm_count - (c.sm_count - 1) % mt_all : c.sm_count;
+  P.single = P.ntiles <= single_cap;
+  if (P.single) {
+    P.tiles_seed = int(P.ntiles);
+    P.grid_seed = int(std::min<int64_t>(c.sm_count, P.ntiles * mt_all));
+    if (mt_all > 1 && P.ntiles * mt_all > P.grid_seed) P.grid_seed -= (P.grid_seed - 1) % mt_all;
+    P.grid_main = 0;
+  } else {
+    // Large corpus: a sampling launch over S tiles spread evenly over the shard (their rows are scored again by the
+    // main launch: S trades that repeat against the sharpness of the starting threshold, K'/(256 S) of the rows pass)
+    const int want = umma_env_int("B2R_SEED_TILES", int(P.ntiles / 40));
+    P.tiles_seed = int(std::min<int64_t>(P.ntiles, std::max(32, std::min(want, c.sm_count))));
+    P.seed_j = P.tiles_seed * 4 >= 3 * c.kp ? 4 : 8;
+    P.grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(P.tiles_seed) * mt_all));
+    P.grid_main = int(std::min<int64_t>(c.sm_count, P.ntiles * mt_all));
+  }
   P.grid_range = int(std::min<int64_t>(c.sm_count, P.ntiles));
-  P.slots = std::max(P.grid_seed + P.grid_main, P.grid_range);
+  P.slots = std::max(P.single ? P.grid_seed : P.grid_main, P.grid_range);
   P.cap = 128;
   while (P.cap < 4 * c.kp) P.cap <<= 1;
   P.kmax = P.cap / 2 - 16;
@@ -756,7 +822,8 @@ inline void umma_fill_finalize(const UmmaState& S, const UmmaPlan& P, int nslots
   fp.q_stride = 0;
 }
 
-// First pass: seed launch(es), threshold selection, main launch(es).
+// First pass.  Small corpus: one launch (in-TMEM bisection).  Large corpus: sampling launch -> seed_thr_kernel ->
+// main launch over every row (the timers bracket the main launch).
 inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
   if (c.nq > kUmMaxLaunch * kUmQMax) { err = "too many queries for one tcgen05 call"; return -5; }
   const UmmaPlan P = umma_plan(c);
@@ -765,7 +832,7 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   const CUtensorMap* tmx = nullptr;
   rc = umma_get_map(S, 0, &tmx, P.f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * P.esz, kUmBN, err);
   if (rc) return rc;
-  const int slots = P.grid_seed + P.grid_main;
+  const int slots = P.single ? P.grid_seed : P.grid_main;
   umma_fill_finalize(S, P, slots, slots, fp);
   fp.errfac = umma_errfac(P.f32, c.split, c.shadow, c.d);
 
@@ -784,52 +851,65 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * slots * P.mt_max * P.cap * 128;
     p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * slots * P.mt_max * 128;
     p.idesc = umma_idesc(P.f32);
+    p.all_tiles = P.ntiles;
 #ifdef B2R_UMMA_PROBE
     p.dbg = c.dbg; p.dbg_flags = c.dbg_flags;
 #endif
-    // seed launch
-    p.row0 = 0; p.ntiles = P.tiles_seed; p.slot_base = 0; p.bisect_first = 1;
-    cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_seed, *tmq[l], *tmqlo[l], *tmx, p, st);
-    if (e != cudaSuccess) { err = std::string("tcgen05 seed launch failed: ") + cudaGetErrorString(e); return -2; }
-    ++*launches;
   }
-  if (P.grid_main > 0) {
-    // thresholds from the seed slots, then the main launch over the remaining rows
-    FinalizeParams sp = fp;
-    sp.nslots = P.grid_seed;
-    sp.kp = c.kp;
-    sp.sortn = 8192;
-    if (!S.attr_set[8]) {
-      cudaError_t ea = cudaFuncSetAttribute(seed_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (8192 + 512) * 8);
-      if (ea != cudaSuccess) { err = std::string("seed_select attribute failed: ") + cudaGetErrorString(ea); return -2; }
-      S.attr_set[8] = true;
-    }
-    seed_select_kernel<<<c.nq, c.nq >= 256 ? 256 : kFinThreads, size_t(sp.sortn + 512) * 8, st>>>(sp, c.thr);   // + tmp[next_pow2(kp) <= 256]
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) { err = std::string("seed_select launch failed: ") + cudaGetErrorString(e); return -2; }
-    ++*launches;
-    if (c.ev_main0) cudaEventRecord(c.ev_main0, st);
-    c.main_rows = c.n - int64_t(P.tiles_seed) * kUmBN;
+  if (P.single) {
     for (int l = 0; l < P.nlaunch; ++l) {
       UmmaParams& p = pp[l];
-      p.row0 = int64_t(P.tiles_seed) * kUmBN; p.ntiles = P.tiles_main; p.slot_base = P.grid_seed; p.bisect_first = 0;
-      e = umma_kernel_launch(S, c, P.f32, P.grid_main, *tmq[l], *tmqlo[l], *tmx, p, st);
-      if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
+      p.row0 = 0; p.ntiles = P.ntiles; p.slot_base = 0; p.bisect_first = 1;
+      cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_seed, *tmq[l], *tmqlo[l], *tmx, p, st);
+      if (e != cudaSuccess) { err = std::string("tcgen05 launch failed: ") + cudaGetErrorString(e); return -2; }
       ++*launches;
     }
-    if (c.ev_main1) cudaEventRecord(c.ev_main1, st);
-  } else {
-    // the seed launch was the whole search
-    c.main_rows = 0;
+    c.main_rows = 0;      // nothing to time separately
+    return 0;
   }
+  // sampling launch + thresholds
+  const int nvals = P.tiles_seed * P.seed_j;
+  const size_t need = size_t(c.nq) * nvals * sizeof(float);
+  if (need > S.seedv_bytes) {
+    if (S.seedv) cudaFree(S.seedv);
+    S.seedv = nullptr; S.seedv_bytes = 0;
+    if (cudaMalloc(&S.seedv, need) != cudaSuccess) { cudaGetLastError(); err = "sample scratch allocation failed"; return -3; }
+    S.seedv_bytes = need;
+  }
+  for (int l = 0; l < P.nlaunch; ++l) {
+    UmmaParams p = pp[l];
+    p.row0 = 0; p.ntiles = P.tiles_seed; p.slot_base = 0; p.bisect_first = 0;
+    p.seed_topj = 1; p.seed_j = P.seed_j; p.seedv = static_cast<float*>(S.seedv);
+    cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_seed, *tmq[l], *tmqlo[l], *tmx, p, st);
+    if (e != cudaSuccess) { err = std::string("tcgen05 sampling launch failed: ") + cudaGetErrorString(e); return -2; }
+    ++*launches;
+  }
+  {
+    const size_t smem = size_t(kSeedThrWarps) * nvals * sizeof(uint32_t);
+    seed_thr_kernel<<<(c.nq + kSeedThrWarps - 1) / kSeedThrWarps, kSeedThrWarps * 32, smem, st>>>(
+        static_cast<const float*>(S.seedv), c.nq, nvals, c.kp, c.thr);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("seed_thr launch failed: ") + cudaGetErrorString(e); return -2; }
+    ++*launches;
+  }
+  if (c.ev_main0) cudaEventRecord(c.ev_main0, st);
+  c.main_rows = c.n;
+  for (int l = 0; l < P.nlaunch; ++l) {
+    UmmaParams& p = pp[l];
+    p.row0 = 0; p.ntiles = P.ntiles; p.slot_base = 0; p.bisect_first = 0;
+    cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_main, *tmq[l], *tmqlo[l], *tmx, p, st);
+    if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
+    ++*launches;
+  }
+  if (c.ev_main1) cudaEventRecord(c.ev_main1, st);
   return 0;
 }
 
 // Range pass (second pass of exact mode): one launch per query chunk over ALL rows, with the fixed thresholds of
 // the compact list; `c` describes the compact query buffers and the engine of this pass (fp32 rows: 3xTF32),
 // `first` the first pass's call (its plan sized the scratch this pass reuses).
-inline int umma_launch_range(UmmaState& S, UmmaCall& c, const UmmaCall& first, cudaStream_t st, FinalizeParams& fp,
-                             int* launches, std::string& err) {
+inline int umma_launch_range(UmmaState& S, UmmaCall& c, const UmmaCall& first, int pass /* 1 or 2 */, cudaStream_t st,
+                             FinalizeParams& fp, int* launches, std::string& err) {
   UmmaPlan P = umma_plan(first);       // same scratch geometry (cap, mt_max, nlaunch, slots) as the first pass
   const bool f32 = c.storage == 0;
   P.f32 = f32; P.esz = f32 ? 4 : 2; P.kelems = f32 ? 32 : 64; P.num_k = (c.d + P.kelems - 1) / P.kelems;
@@ -842,7 +922,7 @@ inline int umma_launch_range(UmmaState& S, UmmaCall& c, const UmmaCall& first, c
     const int nq = std::min(kUmQMax, c.nq - q0);
     const CUtensorMap* tmq = nullptr;
     const CUtensorMap* tmqlo = nullptr;
-    rc = umma_query_maps(S, c, P, 1, l, nq, &tmq, &tmqlo, err);
+    rc = umma_query_maps(S, c, P, pass, l, nq, &tmq, &tmqlo, err);
     if (rc) return rc;
     UmmaParams p{};
     p.n = c.n; p.nq = nq; p.q0 = q0; p.mtiles = (nq + kUmBM - 1) / kUmBM; p.mt_stride = P.mt_max; p.num_k = P.num_k;

@@ -3,13 +3,13 @@
 # usage: tools/ncu_times.sh <batch> <mode> <tag>
 set -u
 B=$1; MODE=$2; TAG=$3
-CMD="python bench.py --steps 2 --warmup 3 --batch $B --mode $MODE --sweep= --no-cpu"
+CMD="python bench.py --steps 2 --warmup 3 --batch $B --mode $MODE --sweep= --extras= --scale-configs= --no-cpu --no-peaks"
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'score_umma|score_fma|finalize|seed_select|prep_queries|merge_packed' -c 60 \
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'score_umma|score_fma|score_exact|finalize|seed_thr|prep_queries|merge_packed' -c 60 \
     --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu.log 2>&1
 python - <<PY
 import csv
 rows=[r for r in csv.reader(open("gpurun_out/${TAG}_launches.csv")) if len(r)>10 and r[0].isdigit()]
-for r in rows[-14:]:
+for r in rows[-20:]:
     print(r[4][:60], r[-1], r[-2])
 PY
