@@ -76,6 +76,7 @@ struct UmmaParams {
   // sampling launch (large corpora): the launch's `ntiles` tiles are spread evenly over all `all_tiles` tiles of the
   // shard; the epilogue keeps no candidate, only the `seed_j` best scores of every (tile, query), from which
   // seed_thr_kernel derives each query's starting threshold.  The main launch then covers every row.
+  int resume;               // later round of a multi-round scan: this CTA's buffers keep what earlier rounds appended
   int seed_topj;
   int seed_j;               // 4 or 8
   int64_t all_tiles;
@@ -130,6 +131,52 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// ---- CTA pair (cta_group::2): two CTAs of a cluster on the two SMs of a TPC share one M=256 MMA -------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cluster address of `local` (a shared::cta address of this CTA) in CTA `cta` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {   // arrivals come from the peer CTA too
+  uint32_t ok;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  } while (!ok);
+}
+// TMA load issued by either CTA of the pair into ITS shared memory, completing on the LEADER's mbarrier
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* tmap, uint32_t leader_bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+// commit of the pair's MMAs: one arrival on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"(uint16_t(3)) : "memory");
+}
+template <bool kTf32>
+__device__ __forceinline__ void tc_mma_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  if (kTf32) {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+  } else {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+
 template <bool kTf32>
 __device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
   if (kTf32) {
@@ -249,7 +296,7 @@ __device__ __forceinline__ void compact_lanes(uint64_t* buf, uint32_t& cnt, floa
 // ---------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------
-template <bool kTf32, bool kL2, bool kSplit>
+template <bool kTf32, bool kL2, bool kSplit, bool kPair>
 __global__ void __launch_bounds__(kUmThreadsSplit, 1)
 score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_qlo,
                   const __grid_constant__ CUtensorMap tmap_x, const UmmaParams p) {
@@ -259,8 +306,15 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   // the host side of the launch, B_lo = x - trunc(x) is computed from the landed tile by 4 splitter warps
   // (element-wise, so the swizzled layout needs no decoding).  Each K-step then issues q_hi.x_hi + q_lo.x_hi +
   // q_hi.x_lo into the same accumulator: fp32-grade scores (dropped term <= 2^-20) at 3x the MMA work.
-  constexpr int kStages = kSplit ? 2 : 4;
-  constexpr int kStageStride = kSplit ? 2 * (kUmABytes + kUmBBytes) : kUmStageBytes;
+  // kPair (cta_group::2, launched as clusters of 2): the pair scores 256 queries (128 per CTA: A, and the TMEM
+  // accumulators, stay per CTA) against one 256-row corpus tile of which each CTA stages HALF (B is shared by the
+  // two tensor cores): stage = A 16K | B/2 16K, 6 stages.  Only the leader (cluster rank 0) issues MMAs (M = 256);
+  // both CTAs' TMA loads complete on the leader's `full` barrier; its commits arrive on both CTAs' `empty` /
+  // `tfull` barriers; both CTAs' epilogue warps release an accumulator on the leader's `tempty` barrier.
+  static_assert(!(kPair && kSplit), "the CTA-pair variant has no 3xTF32 form");
+  constexpr int kStages = kSplit ? 2 : (kPair ? 6 : 4);
+  constexpr int kBStage = kPair ? kUmBBytes / 2 : kUmBBytes;   // corpus bytes this CTA stages per K-step
+  constexpr int kStageStride = kSplit ? 2 * (kUmABytes + kUmBBytes) : kUmABytes + kBStage;
   constexpr int kAloOff = kUmABytes;
   constexpr int kBOff = kSplit ? 2 * kUmABytes : kUmABytes;
   constexpr int kBloOff = kBOff + kUmBBytes;
@@ -282,29 +336,38 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     if (nq == 0) return;              // uniform over the grid: nothing was left unproven (the normal case)
   }
   const int mtiles = (nq + kUmBM - 1) / kUmBM;
+  const uint32_t rank = kPair ? cluster_ctarank() : 0u;
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
   const uint32_t tfull0 = smem_u32(bars + 2 * kStages), tempty0 = smem_u32(bars + 2 * kStages + 2);
   const uint32_t split0 = smem_u32(bars + 2 * kStages + 4);   // kSplit: "B_lo written" per stage
   const uint32_t stage0 = smem_u32(smem);
 
-  for (int i = threadIdx.x; i < kUmQMax; i += blockDim.x) { thr_s[i] = -INFINITY; cnt_s[i] = 0u; }
+  for (int i = threadIdx.x; i < kUmQMax; i += blockDim.x) {
+    thr_s[i] = -INFINITY;
+    cnt_s[i] = (p.resume && i < mtiles * kUmBM) ? p.cnt[size_t(p.slot_base + blockIdx.x) * p.mt_stride * 128 + i] : 0u;
+  }
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, 1);
       if (kSplit) mbar_init(split0 + 8 * s, 4);
     }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, kPair ? 8 : 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_q)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_x)) : "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (kPair) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all(); else __syncthreads();      // the peer's barriers must be initialised before anything lands on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -312,9 +375,9 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   // works on ~gridDim/mtiles neighbouring corpus tiles, so a tile is fetched from HBM once and its re-reads by the
   // other query tiles hit L2 whatever the tile size (a contiguous split would keep gridDim different tiles live
   // at once: 116 MB for fp32 rows of 768, more than L2 holds)
-  const int mitems = mtiles;
+  const int mitems = kPair ? (mtiles + 1) / 2 : mtiles;      // pair: an item covers two query tiles, one per CTA
   const int64_t nitems = p.ntiles * mitems;
-  const int64_t i0 = blockIdx.x, i1 = nitems, istep = gridDim.x;
+  const int64_t i0 = kPair ? blockIdx.x >> 1 : blockIdx.x, i1 = nitems, istep = kPair ? gridDim.x >> 1 : gridDim.x;
   const int kelems = kTf32 ? 32 : 64;   // elements of K per stage
 
   if (warp == 0) {
@@ -323,11 +386,20 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       uint32_t stage = 0, phase = 0;
       for (int64_t item = i0; item < i1; item += istep) {
         const int64_t t = item / mitems;
-        const int m = int(item - t * mitems);
-        const int row = int(p.row0 + (p.seed_topj ? (t * p.all_tiles) / p.ntiles : t) * kUmBN);
+        const int m = kPair ? 2 * int(item - t * mitems) + int(rank) : int(item - t * mitems);
+        const int row = int(p.row0 + (p.seed_topj ? (t * p.all_tiles) / p.ntiles : t) * kUmBN) + (kPair ? int(rank) * (kUmBN / 2) : 0);
         for (int k = 0; k < p.num_k; ++k) {
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
           const uint32_t sa = stage0 + stage * kStageStride;
+          if (kPair) {
+            // both CTAs' boxes complete on the leader's barrier, which expects the bytes of both
+            const uint32_t lead = map_to_cta(full0 + 8 * stage, 0);
+            if (rank == 0) mbar_expect_tx(full0 + 8 * stage, 2 * (kUmABytes + kBStage));
+            tma_load_2d_pair(sa, &tmap_q, lead, k * kelems, m * kUmBM);
+            tma_load_2d_pair(sa + kBOff, &tmap_x, lead, k * kelems, row);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           const bool skip_a = B2R_DBG_FLAG(p, 1) && (item > i0 || k >= kStages);
           mbar_expect_tx(full0 + 8 * stage, kUmBBytes + (skip_a ? 0 : (kSplit ? 2 : 1) * kUmABytes));
           if (!skip_a) {
@@ -340,10 +412,11 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+    // ===================== MMA issuer (pair: the leader CTA only) =====================
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
-    for (int64_t item = i0; item < i1; item += istep) {
-      mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+    for (int64_t item = i0; item < (kPair && rank != 0 ? i0 : i1); item += istep) {
+      if (kPair) mbar_wait_cluster(tempty0 + 8 * acc, acc_phase ^ 1);
+      else mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * kUmBN;
       for (int k = 0; k < p.num_k; ++k) {
@@ -354,8 +427,10 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + kBOff);
 #pragma unroll
           for (int j = 0; j < 4; ++j)   // 4 x 32 bytes of K inside the 128-byte swizzle atom
-            if (!B2R_DBG_FLAG(p, 2) || (k == 0 && j == 0))
-              tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
+            if (!B2R_DBG_FLAG(p, 2) || (k == 0 && j == 0)) {
+              if (kPair) tc_mma_pair<kTf32>(tmem_d, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
+              else tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), db + uint64_t(2 * j), p.idesc, uint32_t((k | j) != 0));
+            }
           if (kSplit) {
             const uint64_t dalo = make_smem_desc(sa + kAloOff), dblo = make_smem_desc(sa + kBloOff);
 #pragma unroll
@@ -364,8 +439,13 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
               tc_mma<kTf32>(tmem_d, da + uint64_t(2 * j), dblo + uint64_t(2 * j), p.idesc, 1u);   // q_hi . x_lo
             }
           }
-          tc_commit(empty0 + 8 * stage);                       // frees the smem stage when the MMAs retire
-          if (k == p.num_k - 1) tc_commit(tfull0 + 8 * acc);   // accumulator complete
+          if (kPair) {
+            tc_commit_pair(empty0 + 8 * stage);                       // frees the stage in both CTAs
+            if (k == p.num_k - 1) tc_commit_pair(tfull0 + 8 * acc);   // both CTAs' halves of the accumulator are complete
+          } else {
+            tc_commit(empty0 + 8 * stage);                       // frees the smem stage when the MMAs retire
+            if (k == p.num_k - 1) tc_commit(tfull0 + 8 * acc);   // accumulator complete
+          }
         }
         __syncwarp();
         if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -409,8 +489,8 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     for (int64_t item = i0; item < i1; item += istep) {
       const int64_t t = item / mitems;
       const int mg = int(item - t * mitems);
-      const int m_first = mg;
-      const int m_last = mg + 1;
+      const int m_first = kPair ? 2 * mg + int(rank) : mg;
+      const int m_last = m_first + 1;
       const bool first_visit = !((seen_m >> mg) & 1u);   // first time this CTA sees these query tiles
       seen_m |= 1u << mg;
       const int64_t row = p.row0 + (p.seed_topj ? (t * p.all_tiles) / p.ntiles : t) * kUmBN;
@@ -547,7 +627,10 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+        if (lane == 0) {
+          if (kPair) mbar_arrive_cluster(map_to_cta(tempty0 + 8 * acc, 0));   // the leader's MMA warp waits for both CTAs
+          else mbar_arrive(tempty0 + 8 * acc);
+        }
         if (valid_q) { thr_s[qi] = thr; cnt_s[qi] = cnt; }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
@@ -561,10 +644,11 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all(); else __syncthreads();      // pair: neither CTA may leave while the other can still reach it
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    if (kPair) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
   }
 }
 
@@ -592,9 +676,11 @@ struct UmmaState {
   void* cand = nullptr; size_t cand_bytes = 0;
   void* cnt = nullptr; size_t cnt_bytes = 0;
   void* seedv = nullptr; size_t seedv_bytes = 0;
-  bool attr_set[9] = {false, false, false, false, false, false, false, false, false};
+  bool attr_set[16] = {};
+  int max_pairs[4] = {0, 0, 0, 0};     // co-resident CTA pairs of the pair kernel's variants (0 = not asked yet)
   // slots: 0 corpus (first pass), 1 corpus (range pass), 2.. query maps: [pass][lo][launch]
-  TmapSlot maps[2 + 3 * 2 * kUmMaxLaunch];
+  TmapSlot maps[3 + 3 * 2 * kUmMaxLaunch];
+  static constexpr int kMapPairX = 2 + 3 * 2 * kUmMaxLaunch;   // corpus map with 128-row boxes (CTA-pair kernel)
   void release() {
     if (cand) cudaFree(cand);
     if (cnt) cudaFree(cnt);
@@ -619,6 +705,7 @@ struct UmmaCall {
   cudaEvent_t ev_main0 = nullptr, ev_main1 = nullptr;   // optional: recorded around the main launch(es)
   int64_t main_rows = 0;                                // out: rows the main launch(es) cover
   // range pass only
+  int max_pairs = 0;                    // first pass: co-resident CTA pairs (filled by umma_launch)
   const uint32_t* list_len = nullptr;   // device: entries in the compact list
   uint32_t* ovf = nullptr;              // device: [nq] overflow flags
 };
@@ -694,6 +781,24 @@ __global__ void __launch_bounds__(kSeedThrWarps * 32) seed_thr_kernel(const floa
   if (lane == 0) thr_g[q] = prefix;     // 0 ("none yet") when fewer than K' values were sampled
 }
 
+// Between the rounds of a multi-round scan (very large shards): thr_g[q] is raised to the K'-th best of ALL
+// candidates appended so far, over every CTA's buffer — far sharper than any single CTA's own K'-th best, so the
+// next (8x larger) round appends only ~8 K' entries per query in total and no buffer ever needs compacting.
+// One CTA per query; the candidates stay where they are.
+__global__ void __launch_bounds__(256) tighten_thr_kernel(FinalizeParams p, uint32_t* thr_g) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* s = reinterpret_cast<uint64_t*>(smem_raw);
+  __shared__ int fill_s;
+  __shared__ int off_s[kFinMaxSlots + 1];
+  const int q = blockIdx.x;
+  const int ql = q % p.qchunk, lq = q / p.qchunk;
+  auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
+  auto cnt_of = [&](int slot) -> int { return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per))); };
+  auto key_of = [&](int slot, int i) -> uint64_t { return p.cand[(blk_of(slot) * p.per + i) * 128 + (ql & 127)]; };
+  const int got = gather_topk(s, p.sortn, p.kp, p.nslots, cnt_of, key_of, thr_g[q], off_s, &fill_s, nullptr, s + p.sortn);
+  if (threadIdx.x == 0 && got == p.kp) atomicMax(thr_g + q, uint32_t(s[p.kp - 1] >> 32));
+}
+
 // Shape of one call's launches and scratch (shared by the first pass and the range pass).
 struct UmmaPlan {
   bool f32; int esz, kelems, num_k; int64_t ntiles;
@@ -701,6 +806,9 @@ struct UmmaPlan {
   int tiles_seed;        // sampled tiles of the sampling launch (large corpora)
   int seed_j;
   int grid_seed, grid_main, grid_range, slots, cap, kmax, nlaunch, mt_max;
+  bool pair;             // first pass on the CTA-pair kernel (cta_group::2): two query tiles per item
+  int nrounds;           // main scan: rounds of growing size (1 unless the shard is very large)
+  int64_t round_end[8];  // tile index where round r ends
 };
 
 inline int umma_env_int(const char* name, int dflt) {
@@ -732,8 +840,32 @@ inline UmmaPlan umma_plan(const UmmaCall& c) {
     const int want = umma_env_int("B2R_SEED_TILES", int(P.ntiles / 40));
     P.tiles_seed = int(std::min<int64_t>(P.ntiles, std::max(32, std::min(want, c.sm_count))));
     P.seed_j = P.tiles_seed * 4 >= 3 * c.kp ? 4 : 8;
-    P.grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(P.tiles_seed) * mt_all));
-    P.grid_main = int(std::min<int64_t>(c.sm_count, P.ntiles * mt_all));
+    // tensor-bound fp32 shapes (several query tiles) go to the CTA-pair kernel: each CTA stages half the corpus tile, a
+    // third less operand traffic per flop (measured: kind::tf32 2.13 -> 2.05 ms at batch 1024 on 1M x 768; kind::f16
+    // loses 6 %, its tensor pipe drops from 89 % to 79 % active, so bf16 rows stay on the single-CTA kernel unless
+    // B2R_PAIR=2 asks); an odd tile count wastes half a pair, accepted from 7 tiles up
+    const int pair_env = umma_env_int("B2R_PAIR", 1);
+    P.pair = !c.split && c.max_pairs > 0 && (pair_env == 2 || (pair_env == 1 && P.f32)) && mt_all >= 2 && (mt_all % 2 == 0 || mt_all >= 7) && c.sm_count >= 2;
+    if (P.pair) {
+      const int mpairs = (mt_all + 1) / 2, pairs_max = std::min(c.max_pairs, c.sm_count / 2);
+      P.grid_seed = 2 * int(std::min<int64_t>(pairs_max, int64_t(P.tiles_seed) * mpairs));
+      P.grid_main = 2 * int(std::min<int64_t>(pairs_max, P.ntiles * mpairs));
+    } else {
+      P.grid_seed = int(std::min<int64_t>(c.sm_count, int64_t(P.tiles_seed) * mt_all));
+      P.grid_main = int(std::min<int64_t>(c.sm_count, P.ntiles * mt_all));
+    }
+  }
+  // Very large shards: the sampled threshold lets K'/(256 S) of ALL rows through — tens of thousands of entries per
+  // query at 100M rows, and every (CTA, query) buffer would be compacted over and over.  The main scan then runs in
+  // rounds of 8x growing size with the thresholds tightened from everything found so far in between (each round
+  // appends ~8 K' entries per query in total).
+  P.nrounds = 1;
+  P.round_end[0] = P.ntiles;
+  if (!P.single && P.ntiles > int64_t(umma_env_int("B2R_ROUND_MIN", 64)) * P.tiles_seed) {
+    int r = 0;
+    for (int64_t e = int64_t(8) * P.tiles_seed; e * 4 < P.ntiles && r < 6; e *= 8) P.round_end[r++] = e;
+    P.round_end[r++] = P.ntiles;
+    P.nrounds = r;
   }
   P.grid_range = int(std::min<int64_t>(c.sm_count, P.ntiles));
   P.slots = std::max(P.single ? P.grid_seed : P.grid_main, P.grid_range);
@@ -763,33 +895,87 @@ inline int umma_scratch(UmmaState& S, const UmmaPlan& P, std::string& err) {
   return 0;
 }
 
-inline cudaError_t umma_kernel_launch(UmmaState& S, const UmmaCall& c, bool f32, int grid, const CUtensorMap& tmq,
-                                      const CUtensorMap& tmqlo, const CUtensorMap& tmx, const UmmaParams& p, cudaStream_t st) {
-  const int variant = (f32 ? 2 : 0) + (c.norm2 ? 1 : 0);
+template <bool TF, bool L2, bool SP, bool PR>
+inline cudaError_t umma_launch_variant(UmmaState& S, int vi, int grid, const CUtensorMap& tmq, const CUtensorMap& tmqlo,
+                                       const CUtensorMap& tmx, const UmmaParams& p, cudaStream_t st) {
   cudaError_t e = cudaSuccess;
-#define B2R_UM_LAUNCH(TF, L2, SP)                                                                                  \
-  do {                                                                                                             \
-    const int vi = variant * 2 + (SP ? 1 : 0);                                                                     \
-    if (!S.attr_set[vi]) {                                                                                         \
-      e = cudaFuncSetAttribute(score_umma_kernel<TF, L2, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes); \
-      if (e == cudaSuccess) S.attr_set[vi] = true;                                                                 \
-    }                                                                                                              \
-    if (e == cudaSuccess)                                                                                          \
-      score_umma_kernel<TF, L2, SP><<<grid, SP ? kUmThreadsSplit : kUmThreads, kUmSmemBytes, st>>>(tmq, tmqlo, tmx, p); \
-  } while (0)
-  if (c.split) {   // 3xTF32: fp32 rows only
-    if (c.norm2) B2R_UM_LAUNCH(true, true, true); else B2R_UM_LAUNCH(true, false, true);
-  } else {
-    if (f32) { if (c.norm2) B2R_UM_LAUNCH(true, true, false); else B2R_UM_LAUNCH(true, false, false); }
-    else     { if (c.norm2) B2R_UM_LAUNCH(false, true, false); else B2R_UM_LAUNCH(false, false, false); }
+  if (!S.attr_set[vi]) {
+    e = cudaFuncSetAttribute(score_umma_kernel<TF, L2, SP, PR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes);
+    if (e != cudaSuccess) return e;
+    S.attr_set[vi] = true;
   }
-#undef B2R_UM_LAUNCH
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(SP ? kUmThreadsSplit : kUmThreads);
+  cfg.dynamicSmemBytes = kUmSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  if (PR) {                      // the two CTAs of a pair must sit on the two SMs of one TPC: a cluster of 2
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+  }
+  return cudaLaunchKernelEx(&cfg, score_umma_kernel<TF, L2, SP, PR>, tmq, tmqlo, tmx, p);
+}
+
+inline cudaError_t umma_kernel_launch(UmmaState& S, const UmmaCall& c, bool f32, int grid, const CUtensorMap& tmq,
+                                      const CUtensorMap& tmqlo, const CUtensorMap& tmx, const UmmaParams& p, cudaStream_t st,
+                                      bool pair = false) {
+  const int variant = (f32 ? 2 : 0) + (c.norm2 ? 1 : 0);
+  cudaError_t e;
+  if (pair) {
+    const int vi = 8 + variant;
+    if (f32) e = c.norm2 ? umma_launch_variant<true, true, false, true>(S, vi, grid, tmq, tmqlo, tmx, p, st)
+                         : umma_launch_variant<true, false, false, true>(S, vi, grid, tmq, tmqlo, tmx, p, st);
+    else     e = c.norm2 ? umma_launch_variant<false, true, false, true>(S, vi, grid, tmq, tmqlo, tmx, p, st)
+                         : umma_launch_variant<false, false, false, true>(S, vi, grid, tmq, tmqlo, tmx, p, st);
+  } else if (c.split) {   // 3xTF32: fp32 rows only
+    const int vi = variant * 2 + 1;
+    e = c.norm2 ? umma_launch_variant<true, true, true, false>(S, vi, grid, tmq, tmqlo, tmx, p, st)
+                : umma_launch_variant<true, false, true, false>(S, vi, grid, tmq, tmqlo, tmx, p, st);
+  } else {
+    const int vi = variant * 2;
+    if (f32) e = c.norm2 ? umma_launch_variant<true, true, false, false>(S, vi, grid, tmq, tmqlo, tmx, p, st)
+                         : umma_launch_variant<true, false, false, false>(S, vi, grid, tmq, tmqlo, tmx, p, st);
+    else     e = c.norm2 ? umma_launch_variant<false, true, false, false>(S, vi, grid, tmq, tmqlo, tmx, p, st)
+                         : umma_launch_variant<false, false, false, false>(S, vi, grid, tmq, tmqlo, tmx, p, st);
+  }
   if (e == cudaSuccess) e = cudaGetLastError();
   return e;
 }
 
-inline uint32_t umma_idesc(bool f32) {
-  return (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) | (uint32_t(kUmBM >> 4) << 24);
+// How many CTA pairs of the pair kernel can be resident at once (asked once per variant).
+inline int umma_max_pairs(UmmaState& S, bool f32, bool l2) {
+  const int variant = (f32 ? 2 : 0) + (l2 ? 1 : 0);
+  if (S.max_pairs[variant] > 0) return S.max_pairs[variant];
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2);
+  cfg.blockDim = dim3(kUmThreads);
+  cfg.dynamicSmemBytes = kUmSmemBytes;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  cudaError_t e;
+#define B2R_PAIR_OCC(TF, L2)                                                                                           \
+  do {                                                                                                                  \
+    e = cudaFuncSetAttribute(score_umma_kernel<TF, L2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kUmSmemBytes); \
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveClusters(&n, score_umma_kernel<TF, L2, false, true>, &cfg);         \
+  } while (0)
+  if (f32) { if (l2) B2R_PAIR_OCC(true, true); else B2R_PAIR_OCC(true, false); }
+  else     { if (l2) B2R_PAIR_OCC(false, true); else B2R_PAIR_OCC(false, false); }
+#undef B2R_PAIR_OCC
+  if (e != cudaSuccess) { cudaGetLastError(); n = 0; }
+  S.max_pairs[variant] = n > 0 ? n : -1;
+  return S.max_pairs[variant];
+}
+
+inline uint32_t umma_idesc(bool f32, bool pair = false) {   // pair: M = 256 over the two CTAs
+  return (1u << 4) | ((f32 ? 2u : 1u) << 7) | ((f32 ? 2u : 1u) << 10) | (uint32_t(kUmBN >> 3) << 17) |
+         (uint32_t((pair ? 2 * kUmBM : kUmBM) >> 4) << 24);
 }
 
 // Query maps of launch l.  Rows are padded to whole 128-query boxes (the buffers are sized for it; rows >= nq only
@@ -826,11 +1012,13 @@ inline void umma_fill_finalize(const UmmaState& S, const UmmaPlan& P, int nslots
 // main launch over every row (the timers bracket the main launch).
 inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParams& fp, int* launches, std::string& err) {
   if (c.nq > kUmMaxLaunch * kUmQMax) { err = "too many queries for one tcgen05 call"; return -5; }
-  const UmmaPlan P = umma_plan(c);
+  c.max_pairs = umma_max_pairs(S, c.storage == 0, c.norm2 != nullptr);
+  const UmmaPlan P = umma_plan(c);       // (no room for clusters, max_pairs < 1: the plan stays on the single-CTA kernel)
   int rc = umma_scratch(S, P, err);
   if (rc) return rc;
   const CUtensorMap* tmx = nullptr;
-  rc = umma_get_map(S, 0, &tmx, P.f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * P.esz, kUmBN, err);
+  if (P.pair) rc = umma_get_map(S, UmmaState::kMapPairX, &tmx, P.f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * P.esz, kUmBN / 2, err);
+  else rc = umma_get_map(S, 0, &tmx, P.f32, c.X, uint64_t(c.ld), uint64_t(c.n), uint64_t(c.ld) * P.esz, kUmBN, err);
   if (rc) return rc;
   const int slots = P.single ? P.grid_seed : P.grid_main;
   umma_fill_finalize(S, P, slots, slots, fp);
@@ -850,7 +1038,7 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     p.kp = c.kp; p.cap = P.cap; p.kmax = P.kmax; p.bmax = std::min(P.cap - 40, std::max(2 * c.kp, c.kp + 56)); p.norm2 = c.norm2; p.thr_g = c.thr;
     p.cand = reinterpret_cast<uint64_t*>(S.cand) + size_t(l) * slots * P.mt_max * P.cap * 128;
     p.cnt = reinterpret_cast<uint32_t*>(S.cnt) + size_t(l) * slots * P.mt_max * 128;
-    p.idesc = umma_idesc(P.f32);
+    p.idesc = umma_idesc(P.f32, P.pair);
     p.all_tiles = P.ntiles;
 #ifdef B2R_UMMA_PROBE
     p.dbg = c.dbg; p.dbg_flags = c.dbg_flags;
@@ -880,7 +1068,7 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
     UmmaParams p = pp[l];
     p.row0 = 0; p.ntiles = P.tiles_seed; p.slot_base = 0; p.bisect_first = 0;
     p.seed_topj = 1; p.seed_j = P.seed_j; p.seedv = static_cast<float*>(S.seedv);
-    cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_seed, *tmq[l], *tmqlo[l], *tmx, p, st);
+    cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_seed, *tmq[l], *tmqlo[l], *tmx, p, st, P.pair);
     if (e != cudaSuccess) { err = std::string("tcgen05 sampling launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
   }
@@ -894,12 +1082,30 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   }
   if (c.ev_main0) cudaEventRecord(c.ev_main0, st);
   c.main_rows = c.n;
-  for (int l = 0; l < P.nlaunch; ++l) {
-    UmmaParams& p = pp[l];
-    p.row0 = 0; p.ntiles = P.ntiles; p.slot_base = 0; p.bisect_first = 0;
-    cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_main, *tmq[l], *tmqlo[l], *tmx, p, st);
-    if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
-    ++*launches;
+  int64_t tile0 = 0;
+  for (int r = 0; r < P.nrounds; ++r) {
+    if (r > 0) {      // thresholds from everything the earlier rounds found
+      FinalizeParams tp = fp;
+      tp.kp = c.kp;
+      tp.sortn = 8192;
+      if (!S.attr_set[12]) {
+        cudaError_t ea = cudaFuncSetAttribute(tighten_thr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (8192 + 512) * 8);
+        if (ea != cudaSuccess) { err = std::string("tighten_thr attribute failed: ") + cudaGetErrorString(ea); return -2; }
+        S.attr_set[12] = true;
+      }
+      tighten_thr_kernel<<<c.nq, 256, size_t(tp.sortn + 512) * 8, st>>>(tp, c.thr);
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) { err = std::string("tighten_thr launch failed: ") + cudaGetErrorString(e); return -2; }
+      ++*launches;
+    }
+    for (int l = 0; l < P.nlaunch; ++l) {
+      UmmaParams& p = pp[l];
+      p.row0 = tile0 * kUmBN; p.ntiles = P.round_end[r] - tile0; p.slot_base = 0; p.bisect_first = 0; p.resume = r > 0;
+      cudaError_t e = umma_kernel_launch(S, c, P.f32, P.grid_main, *tmq[l], *tmqlo[l], *tmx, p, st, P.pair);
+      if (e != cudaSuccess) { err = std::string("tcgen05 main launch failed: ") + cudaGetErrorString(e); return -2; }
+      ++*launches;
+    }
+    tile0 = P.round_end[r];
   }
   if (c.ev_main1) cudaEventRecord(c.ev_main1, st);
   return 0;

@@ -121,6 +121,25 @@ def test_constant_corpus_and_large_k(oracle):
         assert st["exhaustive_queries"] == 9 and st["unverified"] == 0
 
 
+@pytest.mark.parametrize("storage,nq", [("f32", 300), ("bf16", 130), ("f32", 2100)])
+def test_multi_round_scan_of_a_large_shard(oracle, monkeypatch, storage, nq):
+    """Very large shards are scanned in rounds of growing size with the thresholds tightened in between (every
+    CTA's buffers persist from round to round).  The knobs that decide it are lowered here so that a 300k-row
+    corpus takes the same path as a 100M-row one: sampling launch, three rounds, two tightenings."""
+    monkeypatch.setenv("B2R_SEED_TILES", "32")
+    monkeypatch.setenv("B2R_ROUND_MIN", "1")
+    x, q = _data(oracle, 300_000, 128, nq, 63)
+    x[250_000:250_030] = x[9]                       # a tie cluster that only the last round sees
+    q[1] = x[9]
+    idx = b2r.IndexFlatIP(128, storage=storage)
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    xo, qo = (oracle.round_bf16(x), oracle.round_bf16(q)) if storage == "bf16" else (x, q)
+    _check(D, I, *oracle.search_ref(xo, qo, 10, 0, extra=128))
+    st = idx.last_stats()
+    assert st["unverified"] == 0 and st["launches"] >= 11      # prep, sample, thr, 3 rounds + 2 tightenings, merge, ...
+
+
 def test_fallback_counters_add_up_over_query_batches(oracle):
     """A call of more than 8192 queries is walked in batches; an unproven query in the second batch is handled
     there and the counters of the batches add up on the device (no read-back between them)."""

@@ -214,6 +214,19 @@ static int run_perf(int64_t n, int nq, int d, bool f32, int flags, int split, in
     float ms; cudaEventElapsedTime(&ms, e0, e1);
     best = std::min(best, ms);
   }
+  if (const char* sus = getenv("B2R_SUSTAIN_S")) {   // back-to-back launch sets for that long: the power-capped regime
+    const double secs = atof(sus);
+    int reps = std::max(4, int(secs * 1e3 / best)), done = 0;
+    cudaEventRecord(e0);
+    for (; done < reps; ++done) {
+      FinalizeParams fp{}; int launches = 0; std::string err;
+      if (umma_launch(S, c, nullptr, fp, &launches, err)) return 1;
+    }
+    cudaEventRecord(e1);
+    if (cudaDeviceSynchronize() != cudaSuccess) { printf("KERNEL FAULT (sustained)\n"); return 2; }
+    float ms; cudaEventElapsedTime(&ms, e0, e1);
+    printf("sustained %d sets in %.2f s: %.3f ms per set, %.0f TFLOP/s\n", done, ms * 1e-3, ms / done, 2.0 * nq * double(n) * d / (ms / done) / 1e9);
+  }
   const double bytes = double(n) * ld * esz, flops = 2.0 * nq * double(n) * d;
   printf("perf n=%lld nq=%d d=%d %s flags=%d split=%d: %.3f ms  corpus %.2f TB/s  %.0f TFLOP/s\n", (long long)n, nq, d,
          f32 ? "tf32" : "bf16", flags, split, best, bytes / best / 1e9, flops / best / 1e9);
@@ -249,6 +262,10 @@ int main(int argc, char** argv) {
       {256, 128, 32, 16, true, false, true},    // 3xTF32, one K step
       {4096, 70, 384, 16, true, false, true},
       {20000, 200, 768, 16, true, true, true},
+      {50000, 256, 128, 16, false, false},      // CTA-pair kernel (large corpus, even number of query tiles): bf16
+      {50000, 256, 96, 16, true, false},        // ... tf32
+      {45000, 900, 64, 16, false, true},        // ... 8 query tiles (the last one ragged), L2
+      {41000, 1000, 32, 16, true, true},
   };
   int only = argc > 1 ? atoi(argv[1]) : -1;
   int idx = 0;
