@@ -556,12 +556,12 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   uint32_t* fb = static_cast<uint32_t*>(idx->fb.p);
   {
     const int blocks = int(std::min<int64_t>((nq + 7) / 8, int64_t(idx->sm_count) * 8));
-    prep_queries_kernel<<<blocks, 256, 0, st>>>(q_dev, nq, int(idx->d), ldq, normalize_queries,
-                                                idx->storage == B2R_STORE_BF16, static_cast<float*>(idx->qf.p),
-                                                (idx->storage == B2R_STORE_BF16 || use_shadow) ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
-                                                static_cast<float*>(idx->qn2.p), split ? static_cast<float*>(idx->qlo.p) : nullptr,
-                                                static_cast<uint32_t*>(idx->thr.p),
-                                                clear_stats ? static_cast<unsigned long long*>(idx->stats.p) : nullptr, fb);
+    CU_TRY(launch_pdl(prep_queries_kernel, blocks, 256, 0, st, q_dev, nq, int(idx->d), ldq, normalize_queries,
+                      int(idx->storage == B2R_STORE_BF16), static_cast<float*>(idx->qf.p),
+                      (idx->storage == B2R_STORE_BF16 || use_shadow) ? static_cast<__nv_bfloat16*>(idx->qh.p) : nullptr,
+                      static_cast<float*>(idx->qn2.p), split ? static_cast<float*>(idx->qlo.p) : nullptr,
+                      static_cast<uint32_t*>(idx->thr.p),
+                      clear_stats ? static_cast<unsigned long long*>(idx->stats.p) : nullptr, fb));
     CU_TRY(cudaGetLastError());
     ++launches;
   }
@@ -636,8 +636,8 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   }
   const size_t smem = size_t(fp.sortn + host_next_pow2(kp)) * 8;
   RC_TRY(smem_attr_once(idx->device, kAttrFinalize + (f32 ? 0 : 1)));
-  if (f32) finalize_kernel<float><<<int(nq), fin_threads, smem, st>>>(fp);
-  else finalize_kernel<__nv_bfloat16><<<int(nq), fin_threads, smem, st>>>(fp);
+  if (f32) CU_TRY(launch_pdl(finalize_kernel<float>, int(nq), fin_threads, smem, st, fp));
+  else CU_TRY(launch_pdl(finalize_kernel<__nv_bfloat16>, int(nq), fin_threads, smem, st, fp));
   CU_TRY(cudaGetLastError());
   ++launches;
 
@@ -661,8 +661,8 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
       const size_t rsmem = size_t(rp.sortn + kRangeKeep) * 8;
       RC_TRY(smem_attr_once(idx->device, kAttrRange + (f32 ? 0 : 1)));
       const int rgrid = int(std::min<int64_t>(nq, int64_t(idx->sm_count) * 2));
-      if (f32) finalize_range_kernel<float><<<rgrid, kFinThreads, rsmem, st>>>(rp);
-      else finalize_range_kernel<__nv_bfloat16><<<rgrid, kFinThreads, rsmem, st>>>(rp);
+      if (f32) CU_TRY(launch_pdl(finalize_range_kernel<float>, rgrid, kFinThreads, rsmem, st, rp));
+      else CU_TRY(launch_pdl(finalize_range_kernel<__nv_bfloat16>, rgrid, kFinThreads, rsmem, st, rp));
       CU_TRY(cudaGetLastError());
       ++launches;
       return B2R_OK;
@@ -785,7 +785,8 @@ static int merge_launch(int metric, int64_t G, int64_t nq, int64_t k, const uint
                         int64_t* I, int device, cudaStream_t st) {
   const int sortn = std::max(4096, host_next_pow2(int(k) + 2048));   // gather rounds append up to 2048 keys
   RC_TRY(smem_attr_once(device, kAttrMerge));
-  merge_packed_kernel<<<int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st>>>(packed, int(G), int(nq), int(k), g_stride, sortn, metric, D, I);
+  CU_TRY(launch_pdl(merge_packed_kernel, int(nq), 256, size_t(sortn + host_next_pow2(int(k))) * 8, st, packed, int(G), int(nq),
+                    int(k), g_stride, sortn, metric, D, I));
   CU_TRY(cudaGetLastError());
   return B2R_OK;
 }

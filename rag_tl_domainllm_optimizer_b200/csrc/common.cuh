@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 namespace b2r {
 
@@ -183,6 +184,37 @@ __device__ __forceinline__ void warp_bitonic64_desc(uint64_t& k0, uint64_t& k1, 
       }
     }
   }
+}
+
+// ---------------------------------------------------------------------------------
+// Programmatic dependent launch: the kernels of one search are launched with the
+// programmatic-serialization attribute; each starts by letting ITS successor be scheduled
+// and then waits for its predecessor to complete (and its writes to be visible) before it
+// reads or writes global memory.  The successor's launch latency and prologue thus overlap
+// the predecessor's tail.  Both instructions are no-ops in a kernel launched the plain way.
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;\ngriddepcontrol.wait;" ::: "memory");
+}
+
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* v = getenv("B2R_PDL"); return !(v && v[0] == '0'); }();
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 __device__ __forceinline__ int next_pow2(int v) {

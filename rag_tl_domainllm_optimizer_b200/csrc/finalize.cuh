@@ -318,6 +318,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
   __shared__ int off_s[kFinMaxSlots + 1];
   __shared__ int handover_s;                              // -1: proven; >= 0: entry in the range list; -2: exhaustive list
   const int q = blockIdx.x, tid = threadIdx.x;
+  pdl_enter();
 
   const uint32_t thrq = p.thr ? p.thr[q] : 0u;
   const int ql = p.interleave ? q % p.qchunk : 0, lq = p.interleave ? q / p.qchunk : 0;
@@ -403,6 +404,7 @@ __global__ void __launch_bounds__(kFinThreads) finalize_range_kernel(FinalizePar
   __shared__ int off_s[kFinMaxSlots + 1];
   const int tid = threadIdx.x;
   __shared__ int next_s;
+  pdl_enter();
   const int n1 = int(min(*p.cur.n, uint32_t(p.nq)));
   for (int e = blockIdx.x; e < n1; e += gridDim.x) {
     const int q = int(p.cur.q[e]);
@@ -457,6 +459,7 @@ __global__ void __launch_bounds__(256) merge_packed_kernel(const uint64_t* __res
   __shared__ int fill_s;
   __shared__ int off_s[kFinMaxSlots + 1];
   const int q = blockIdx.x;
+  pdl_enter();
   auto cnt_of = [&](int) -> int { return k; };
   auto key_of = [&](int g, int i) -> uint64_t { return packed[int64_t(g) * g_stride + int64_t(q) * k + i]; };
   const int got = gather_topk(s, sortn, k, G, cnt_of, key_of, 0u, off_s, &fill_s, nullptr, s + sortn);

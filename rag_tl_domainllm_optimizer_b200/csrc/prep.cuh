@@ -146,6 +146,7 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
                                                            uint32_t* __restrict__ thr /* [nq] cleared */,
                                                            unsigned long long* __restrict__ stats /* [4] cleared if asked */,
                                                            uint32_t* __restrict__ fb /* [4] list counters, cleared */) {
+  pdl_enter();
   // the per-search thresholds, counters and hand-over lists start at zero: cleared here instead of by memset launches
   if (stats && blockIdx.x == 0 && threadIdx.x < 4) stats[threadIdx.x] = 0ull;
   if (fb && blockIdx.x == 0 && threadIdx.x < 4) fb[threadIdx.x] = 0u;

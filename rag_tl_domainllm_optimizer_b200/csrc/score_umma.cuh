@@ -328,6 +328,7 @@ score_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_enter();
   // queries of this launch: fixed by the host, or (range mode) this launch's share of the device-side list
   int nq = p.nq;
   if (p.range) {
@@ -765,6 +766,7 @@ __global__ void __launch_bounds__(kSeedThrWarps * 32) seed_thr_kernel(const floa
   extern __shared__ uint32_t sk_all[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = blockIdx.x * kSeedThrWarps + warp;
+  pdl_enter();
   if (q >= nq) return;
   uint32_t* sk = sk_all + size_t(warp) * nvals;
   const float* v = seedv + size_t(q) * nvals;
@@ -791,6 +793,7 @@ __global__ void __launch_bounds__(256) tighten_thr_kernel(FinalizeParams p, uint
   __shared__ int fill_s;
   __shared__ int off_s[kFinMaxSlots + 1];
   const int q = blockIdx.x;
+  pdl_enter();
   const int ql = q % p.qchunk, lq = q / p.qchunk;
   auto blk_of = [&](int slot) -> size_t { return (size_t(lq) * p.slot_total + slot) * p.mt_max + (ql >> 7); };
   auto cnt_of = [&](int slot) -> int { return int(min(p.cnt[blk_of(slot) * 128 + (ql & 127)], uint32_t(p.per))); };
@@ -909,13 +912,20 @@ inline cudaError_t umma_launch_variant(UmmaState& S, int vi, int grid, const CUt
   cfg.blockDim = dim3(SP ? kUmThreadsSplit : kUmThreads);
   cfg.dynamicSmemBytes = kUmSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
+  int na = 0;
   if (PR) {                      // the two CTAs of a pair must sit on the two SMs of one TPC: a cluster of 2
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = 2; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+    ++na;
   }
+  if (pdl_enabled()) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = na;
   return cudaLaunchKernelEx(&cfg, score_umma_kernel<TF, L2, SP, PR>, tmq, tmqlo, tmx, p);
 }
 
@@ -1074,9 +1084,9 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
   }
   {
     const size_t smem = size_t(kSeedThrWarps) * nvals * sizeof(uint32_t);
-    seed_thr_kernel<<<(c.nq + kSeedThrWarps - 1) / kSeedThrWarps, kSeedThrWarps * 32, smem, st>>>(
-        static_cast<const float*>(S.seedv), c.nq, nvals, c.kp, c.thr);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = launch_pdl(seed_thr_kernel, (c.nq + kSeedThrWarps - 1) / kSeedThrWarps, kSeedThrWarps * 32, smem, st,
+                               static_cast<const float*>(S.seedv), c.nq, nvals, c.kp, c.thr);
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("seed_thr launch failed: ") + cudaGetErrorString(e); return -2; }
     ++*launches;
   }
@@ -1093,8 +1103,8 @@ inline int umma_launch(UmmaState& S, UmmaCall& c, cudaStream_t st, FinalizeParam
         if (ea != cudaSuccess) { err = std::string("tighten_thr attribute failed: ") + cudaGetErrorString(ea); return -2; }
         S.attr_set[12] = true;
       }
-      tighten_thr_kernel<<<c.nq, 256, size_t(tp.sortn + 512) * 8, st>>>(tp, c.thr);
-      cudaError_t e = cudaGetLastError();
+      cudaError_t e = launch_pdl(tighten_thr_kernel, c.nq, 256, size_t(tp.sortn + 512) * 8, st, tp, c.thr);
+      if (e == cudaSuccess) e = cudaGetLastError();
       if (e != cudaSuccess) { err = std::string("tighten_thr launch failed: ") + cudaGetErrorString(e); return -2; }
       ++*launches;
     }
