@@ -604,8 +604,9 @@ static int search_device(b2r_index* idx, int64_t nq, const float* q_dev, int64_t
   }
   fp.thr = static_cast<const uint32_t*>(idx->thr.p);
   fp.nq = int(nq); fp.kp = kp; fp.k = int(k);
-  // few queries: one big CTA per query (latency); many queries: small CTAs, several per SM (throughput)
-  const int fin_threads = nq >= 256 ? 256 : kFinThreads;
+  // few queries: one big CTA per query (latency: more warps re-scoring the K' rows at once); many queries: small CTAs,
+  // several per SM (throughput)
+  const int fin_threads = nq <= idx->sm_count ? kFinThreads : nq <= 4 * idx->sm_count ? 512 : 256;
   fp.sortn = std::max(4096, host_next_pow2(kp + 2048));   // gather rounds append up to 2048 keys
   fp.X = idx->X; fp.ld = idx->ld; fp.d = int(idx->d); fp.storage = idx->storage;
   fp.Q = static_cast<const float*>(idx->qf.p); fp.ldq = ldq; fp.qn2 = static_cast<const float*>(idx->qn2.p);

@@ -125,6 +125,40 @@ __device__ __forceinline__ double warp_reduce64(const TA* a, const TB* b, int d,
   return butterfly64(acc);
 }
 
+// R rows against one query at once: the same per-row arithmetic as warp_reduce64 (a lane folds ITS elements of a
+// row in increasing j; which rows share a trip changes nothing), but the R rows' loads are in flight together and
+// the query chunk is loaded once — for re-scoring candidate rows scattered over HBM one latency at a time.
+template <Red Rd, int R, typename TA, typename TB>
+__device__ __forceinline__ void warp_reduce64_rows(const TA* a, const TB* const (&b)[R], int d, int lane, double (&out)[R]) {
+  double acc[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) acc[r] = 0.0;
+#pragma unroll 2
+  for (int c = lane * 4; c < d; c += 128) {
+    if (c + 4 <= d) {
+      const float4 va = ld4(a + c);
+      float4 vb[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) vb[r] = ld4(b[r] + c);
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        acc[r] = fold1<Rd>(acc[r], va.x, vb[r].x);
+        acc[r] = fold1<Rd>(acc[r], va.y, vb[r].y);
+        acc[r] = fold1<Rd>(acc[r], va.z, vb[r].z);
+        acc[r] = fold1<Rd>(acc[r], va.w, vb[r].w);
+      }
+    } else {
+      for (int j = c; j < d; ++j) {
+        const float aj = ld_elem(a, j);
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = fold1<Rd>(acc[r], aj, ld_elem(b[r], j));
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) out[r] = butterfly64(acc[r]);
+}
+
 // Same reduction when rows are not known to be 16-byte aligned (caller-owned arrays).
 template <Red R>
 __device__ __forceinline__ double warp_reduce64_unaligned(const float* a, const float* b, int d, int lane) {

@@ -254,8 +254,9 @@ __device__ __forceinline__ int gather_topk(uint64_t* s, int sortn, int keep, int
 
 
 // The prepared row of a handed-on query travels to slot e of the list's compact buffers (block-collective).
-__device__ __forceinline__ void copy_query_row(const FbList& L, int e, const float* qrow, int ldq) {
-  for (int c = threadIdx.x * 4; c < ldq; c += blockDim.x * 4) {
+__device__ __forceinline__ void copy_query_row(const FbList& L, int e, const float* qrow, int ldq, int tid = threadIdx.x,
+                                               int nt = blockDim.x) {
+  for (int c = tid * 4; c < ldq; c += nt * 4) {
     const float4 v = ld4(qrow + c);
     if (L.qc_f) st4(L.qc_f + int64_t(e) * ldq + c, v);
     if (L.qc_h) st4(L.qc_h + int64_t(e) * ldq + c, v);
@@ -271,8 +272,9 @@ __device__ __forceinline__ void copy_query_row(const FbList& L, int e, const flo
 }
 
 // Rows [0, min(k, ncand)) of the sorted exact keys -> D/I (or packed keys) of query q; the tail is padded.
-__device__ __forceinline__ void write_topk(const FinalizeParams& p, int q, const uint64_t* s2, int ncand) {
-  for (int j = threadIdx.x; j < p.k; j += blockDim.x) {
+__device__ __forceinline__ void write_topk(const FinalizeParams& p, int q, const uint64_t* s2, int ncand, int tid = threadIdx.x,
+                                           int nt = blockDim.x) {
+  for (int j = tid; j < p.k; j += nt) {
     const bool have = j < ncand;
     uint64_t key = have ? s2[j] : 0ull;
     if (p.packed) {
@@ -293,19 +295,86 @@ __device__ __forceinline__ void rescore_keys(const FinalizeParams& p, const floa
                                              uint64_t* s2) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const T* X = reinterpret_cast<const T*>(p.X);
-  for (int j = warp; j < ncand; j += nwarp) {
-    uint32_t id = key_id(s[j]);
-    const T* xrow = X + int64_t(id) * p.ld;
-    uint64_t key;
-    if (p.metric == 0) {
-      float out = float(warp_reduce64<Red::kDot>(qrow, xrow, p.d, lane));
-      key = make_key_max(out, id);
-    } else {
-      float out = float(warp_reduce64<Red::kSqDiff>(qrow, xrow, p.d, lane));
-      key = make_key_min(out, id);
+  const int row_lines = (p.d * int(sizeof(T)) + 127) / 128;     // 128-byte lines of a stored row
+  // candidate rows sit at random places of the shard (HBM latency each): the rows this warp scores next are pulled
+  // into L2 while it folds the current one
+  auto prefetch_row = [&](int j) {
+    if (j < ncand) {
+      const char* r = reinterpret_cast<const char*>(X + int64_t(key_id(s[j])) * p.ld);
+      for (int l = lane; l < row_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(r + size_t(l) * 128));
     }
-    if (lane == 0) s2[j] = key;
+  };
+  if (ncand <= nwarp) {              // a row per warp at most (few queries, big CTAs): nothing to overlap
+    if (warp < ncand) {
+      const uint32_t id = key_id(s[warp]);
+      const T* xrow = X + int64_t(id) * p.ld;
+      const uint64_t key = p.metric == 0 ? make_key_max(float(warp_reduce64<Red::kDot>(qrow, xrow, p.d, lane)), id)
+                                         : make_key_min(float(warp_reduce64<Red::kSqDiff>(qrow, xrow, p.d, lane)), id);
+      if (lane == 0) s2[warp] = key;
+    }
+    return;
   }
+  // four of the warp's rows per trip: their loads are in flight together (same arithmetic per row as one at a time)
+  prefetch_row(warp + 4 * nwarp);
+  for (int j0 = warp; j0 < ncand; j0 += 4 * nwarp) {
+    prefetch_row(j0 + 8 * nwarp);
+    uint32_t id[4];
+    const T* xrow[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int j = j0 + r * nwarp;
+      id[r] = key_id(s[j < ncand ? j : j0]);
+      xrow[r] = X + int64_t(id[r]) * p.ld;
+    }
+    double out[4];
+    if (p.metric == 0) warp_reduce64_rows<Red::kDot, 4>(qrow, xrow, p.d, lane, out);
+    else warp_reduce64_rows<Red::kSqDiff, 4>(qrow, xrow, p.d, lane, out);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int j = j0 + r * nwarp;
+      if (lane == 0 && j < ncand) s2[j] = p.metric == 0 ? make_key_max(float(out[r]), id[r]) : make_key_min(float(out[r]), id[r]);
+    }
+  }
+}
+
+// Completeness proof of query q (one thread): `amin` is the approximate score of the K'-th kept candidate (every
+// excluded row scored at most that), `kth` the exact key of the k-th returned row.  A query that cannot be proven is
+// counted and appended to the next list (or to the exhaustive list); returns its entry in p.next, else -1.
+__device__ __forceinline__ int prove_or_hand_over(const FinalizeParams& p, int q, float amin_f, uint64_t kth) {
+  const double amin = double(amin_f);
+  const double qn = double(p.qn2[q]), xn = double(*p.maxnorm2);
+  const double nn = sqrt(qn * xn);
+  const double l2x = 2.4e-7 * (xn + qn + nn);            // L2: rounding of the stored norms and of |q|^2
+  bool verified;
+  double base, e_fix;     // a row of the true top-k scores >= base - (errfac * nn + e_fix) in a pass with error factor errfac
+  if (p.metric == 0) {
+    const float sk = key_score_max(kth);
+    verified = float(amin + double(p.errfac) * nn) < sk;                 // any excluded row scores <= that bound
+    base = double(sk);
+    e_fix = 1.2e-7 * nn;                                                 // half an ulp of s_k: keys compare rounded scores
+  } else {
+    const float dk = key_score_min(kth);
+    verified = float(qn - 2.0 * (amin + double(p.errfac) * nn + l2x)) > dk;   // any excluded row is at least that far
+    base = 0.5 * (qn - double(dk));
+    e_fix = 1.5 * l2x;
+  }
+  if (verified) return -1;
+  atomicAdd(p.stats, 1ull);
+  if (p.next.n) {
+    const int e = int(atomicAdd(p.next.n, 1u));
+    p.next.q[e] = uint32_t(q);
+    p.next.thr[e] = f32_to_ordered(__double2float_rd(base - (double(p.errfac_range) * nn + e_fix)));
+    p.next.thr_next[e] = f32_to_ordered(__double2float_rd(base - (double(p.errfac_range2) * nn + e_fix)));
+    p.next.ovf[e] = 0u;
+    return e;
+  }
+  if (p.ex_n) {
+    p.ex_q[atomicAdd(p.ex_n, 1u)] = uint32_t(q);
+    atomicAdd(p.stats + 2, 1ull);
+  } else {
+    atomicAdd(p.stats + 3, 1ull);
+  }
+  return -1;
 }
 
 template <typename T>
@@ -343,45 +412,9 @@ __global__ void __launch_bounds__(kFinThreads) finalize_kernel(FinalizeParams p)
   write_topk(p, q, s2, ncand);
 
   // completeness proof (thread 0)
-  if (tid == 0) {
-    int handover = -1;
-    if (p.stats && ncand == p.kp && p.n > p.kp) {           // the list is full, rows may have been filtered out
-      const int kk = p.k < ncand ? p.k : ncand;
-      const double amin = double(key_score_max(s[p.kp - 1]));
-      const double qn = double(p.qn2[q]), xn = double(*p.maxnorm2);
-      const double nn = sqrt(qn * xn);
-      const double l2x = 2.4e-7 * (xn + qn + nn);            // L2: rounding of the stored norms and of |q|^2
-      bool verified;
-      double base, e_fix;     // a row of the true top-k scores >= base - (errfac * nn + e_fix) in a pass with error factor errfac
-      if (p.metric == 0) {
-        const float sk = key_score_max(s2[kk - 1]);
-        verified = float(amin + double(p.errfac) * nn) < sk;                 // any excluded row scores <= that bound
-        base = double(sk);
-        e_fix = 1.2e-7 * nn;                                                 // half an ulp of s_k: keys compare rounded scores
-      } else {
-        const float dk = key_score_min(s2[kk - 1]);
-        verified = float(qn - 2.0 * (amin + double(p.errfac) * nn + l2x)) > dk;   // any excluded row is at least that far
-        base = 0.5 * (qn - double(dk));
-        e_fix = 1.5 * l2x;
-      }
-      if (!verified) {
-        atomicAdd(p.stats, 1ull);
-        if (p.next.n) {
-          handover = int(atomicAdd(p.next.n, 1u));
-          p.next.q[handover] = uint32_t(q);
-          p.next.thr[handover] = f32_to_ordered(__double2float_rd(base - (double(p.errfac_range) * nn + e_fix)));
-          p.next.thr_next[handover] = f32_to_ordered(__double2float_rd(base - (double(p.errfac_range2) * nn + e_fix)));
-          p.next.ovf[handover] = 0u;
-        } else if (p.ex_n) {
-          p.ex_q[atomicAdd(p.ex_n, 1u)] = uint32_t(q);
-          atomicAdd(p.stats + 2, 1ull);
-        } else {
-          atomicAdd(p.stats + 3, 1ull);
-        }
-      }
-    }
-    handover_s = handover;
-  }
+  if (tid == 0)
+    handover_s = (p.stats && ncand == p.kp && p.n > p.kp)        // the list is full, rows may have been filtered out
+                     ? prove_or_hand_over(p, q, key_score_max(s[p.kp - 1]), s2[(p.k < ncand ? p.k : ncand) - 1]) : -1;
   if (!p.next.n) return;     // uniform
   __syncthreads();
   const int e = handover_s;

@@ -840,7 +840,11 @@ inline UmmaPlan umma_plan(const UmmaCall& c) {
   } else {
     // Large corpus: a sampling launch over S tiles spread evenly over the shard (their rows are scored again by the
     // main launch: S trades that repeat against the sharpness of the starting threshold, K'/(256 S) of the rows pass)
-    const int want = umma_env_int("B2R_SEED_TILES", int(P.ntiles / 40));
+    // S is chosen in whole waves of the grid: about 1/40 of the scan's items, at least one wave (one query tile: all
+    // 148 SMs take one sampled tile each — a sharper threshold for free)
+    const int64_t items_want = std::max<int64_t>(1, P.ntiles * mt_all / 40);
+    const int waves = int(std::max<int64_t>(1, (items_want + c.sm_count / 2) / c.sm_count));
+    const int want = umma_env_int("B2R_SEED_TILES", int(int64_t(waves) * c.sm_count / mt_all));
     P.tiles_seed = int(std::min<int64_t>(P.ntiles, std::max(32, std::min(want, c.sm_count))));
     P.seed_j = P.tiles_seed * 4 >= 3 * c.kp ? 4 : 8;
     // tensor-bound fp32 shapes (several query tiles) go to the CTA-pair kernel: each CTA stages half the corpus tile, a
@@ -872,8 +876,9 @@ inline UmmaPlan umma_plan(const UmmaCall& c) {
   }
   P.grid_range = int(std::min<int64_t>(c.sm_count, P.ntiles));
   P.slots = std::max(P.single ? P.grid_seed : P.grid_main, P.grid_range);
+  // entries per (CTA, query) buffer: a compaction keeps between K' and kmax = cap/2 - 16 of them, so cap >= 2K' + 32
   P.cap = 128;
-  while (P.cap < 4 * c.kp) P.cap <<= 1;
+  while (P.cap < 2 * c.kp + 32) P.cap <<= 1;
   P.kmax = P.cap / 2 - 16;
   P.nlaunch = (c.nq + kUmQMax - 1) / kUmQMax;
   P.mt_max = mt_all;
