@@ -42,7 +42,68 @@ __global__ void __launch_bounds__(256) ingest_rows_kernel(const float* __restric
   const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
   const bool vec_in = ((d & 3) == 0) && ((reinterpret_cast<uintptr_t>(in) & 15) == 0);
   float wmax = 0.f;
-  for (int64_t r = warp0; r < n; r += nwarps) {
+  constexpr int kRegChunks = 8;                     // rows of up to 1024 elements stay in registers: read ONCE
+  if (ld <= kRegChunks * 128) {
+    const int nch = (ld + 127) / 128;
+    for (int64_t r = warp0; r < n; r += nwarps) {
+      const float* x = in + r * int64_t(d);
+      TOut* y = out + r * int64_t(ld);
+      float4 v[kRegChunks];
+#pragma unroll
+      for (int t = 0; t < kRegChunks; ++t) {
+        const int c = lane * 4 + t * 128;
+        v[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (t < nch && c < ld) {
+          if (c + 4 <= d && vec_in) {
+            v[t] = __ldcs(reinterpret_cast<const float4*>(x + c));      // streamed: the caller's rows are not read again
+          } else {
+            if (c + 0 < d) v[t].x = x[c + 0];
+            if (c + 1 < d) v[t].y = x[c + 1];
+            if (c + 2 < d) v[t].z = x[c + 2];
+            if (c + 3 < d) v[t].w = x[c + 3];
+          }
+        }
+      }
+      float nrm = 1.f;
+      if (normalize) {                               // DOT64 order: a lane folds ITS elements in increasing j (zeros beyond d add nothing)
+        double ss = 0.0;
+#pragma unroll
+        for (int t = 0; t < kRegChunks; ++t) {
+          const int c = lane * 4 + t * 128;
+          if (t < nch) {
+            if (c + 0 < d) ss = fma(double(v[t].x), double(v[t].x), ss);
+            if (c + 1 < d) ss = fma(double(v[t].y), double(v[t].y), ss);
+            if (c + 2 < d) ss = fma(double(v[t].z), double(v[t].z), ss);
+            if (c + 3 < d) ss = fma(double(v[t].w), double(v[t].w), ss);
+          }
+        }
+        nrm = float(sqrt(butterfly64(ss)));
+        if (nrm == 0.f) nrm = 1.f;
+      }
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < kRegChunks; ++t) {
+        const int c = lane * 4 + t * 128;
+        if (t < nch && c < ld) {
+          float4 w = v[t];
+          if (normalize) { w.x = w.x / nrm; w.y = w.y / nrm; w.z = w.z / nrm; w.w = w.w / nrm; }
+          w.x = round_store(w.x, y); w.y = round_store(w.y, y); w.z = round_store(w.z, y); w.w = round_store(w.w, y);
+          st4(y + c, w);
+          if (c + 0 < d) acc = fma(double(w.x), double(w.x), acc);
+          if (c + 1 < d) acc = fma(double(w.y), double(w.y), acc);
+          if (c + 2 < d) acc = fma(double(w.z), double(w.z), acc);
+          if (c + 3 < d) acc = fma(double(w.w), double(w.w), acc);
+        }
+      }
+      acc = butterfly64(acc);
+      const float n2 = float(acc);
+      if (norm2 && lane == 0) norm2[r] = n2;
+      wmax = fmaxf(wmax, n2);
+    }
+    if (maxnorm2 && lane == 0 && wmax > 0.f) atomicMax(reinterpret_cast<int*>(maxnorm2), __float_as_int(wmax));
+    return;
+  }
+  for (int64_t r = warp0; r < n; r += nwarps) {      // long rows: norm first, then a second pass (it hits L1/L2)
     const float* x = in + r * int64_t(d);
     TOut* y = out + r * int64_t(ld);
     float nrm = 1.f;
