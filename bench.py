@@ -16,7 +16,7 @@ every search ends with one NCCL all-gather of the packed shard-local top-k plus 
   cpu_baseline : the oracle's FAISS-CPU-like fp32 search ("port") on this box's host cores, bounded sample
   parity    : rank 0 checks the first queries of the timed result against the CPU oracle (all N)
   sweep     : other batch sizes; `extras`: L2 metric, the 3xTF32 engine, clustered / duplicate-laden corpora
-  scale_configs : (--gpus N > 1, or --scale-configs) BASELINE.json configs[4] and configs[2] at full size
+  scale_configs : BASELINE.json configs[0], [4], [2] and [3] at FULL size (every N; --scale-configs picks), each with parity
 
 `--impl reference` times the CPU path alone (rank 0 only) and prints the same line with "impl": "reference".
 """
@@ -502,7 +502,7 @@ def main():
                 q64 = q_dev[:nc].bfloat16().double()
             best_s = torch.full((nc, kc), -float("inf"), dtype=torch.float64, device=device)
             best_i = torch.zeros((nc, kc), dtype=torch.int64, device=device)
-            step_rows = 262144
+            step_rows = max(16384, (1 << 28) // d)      # fp64 copy of a chunk stays near 2 GB
             for r0 in range(lo, hi, step_rows):
                 m = min(step_rows, hi - r0)
                 xb = torch.empty((m, d), dtype=torch.float32, device=device)
@@ -729,7 +729,7 @@ def main():
     scale = []
     # default: both, at every N (the driver's 1/2/4/8 scaling run then carries them), unless the run is already long
     t_run = max_over_ranks(time.perf_counter() - T_START)      # the same decision on every rank
-    which = args.scale_configs if args.scale_configs is not None else ("c5,c3" if t_run < 400 else "")
+    which = args.scale_configs if args.scale_configs is not None else ("c1,c5,c3,c4" if t_run < 400 else "")
     for name in [v for v in which.split(",") if v]:
         if name == "c5":      # configs[4]: 100M x 768 bf16, batch 4096, k=10
             shape = dict(rows=100_000_000, d=768, batch=4096, k=10, mode="bf16")
@@ -737,12 +737,15 @@ def main():
             shape = dict(rows=10_000_000, d=1024, batch=256, k=100, mode="exact")
         elif name == "c4":    # configs[3]: 5M x 4096, 256 queries, k=4
             shape = dict(rows=5_000_000, d=4096, batch=256, k=4, mode="bf16")
+        elif name == "c1":    # configs[0]: 10k x 384, 64 queries, k=5, exact (launch-bound: q/s and us per search)
+            shape = dict(rows=10_000, d=384, batch=64, k=5, mode="exact")
         else:
             continue
         try:
             r = run_config(shape["rows"], shape["d"], shape["batch"], shape["k"], shape["mode"], "ip", "gauss", 0,
-                           steps=5, warmup=3, e2e=False, parity_queries=8 if not args.no_cpu else 0, host_rows_ok=False,
-                           sample_clocks=True)
+                           steps=200 if name == "c1" else 5, warmup=3, e2e=False, parity_queries=8 if not args.no_cpu else 0,
+                           host_rows_ok=shape["rows"] <= 2_000_000, sample_clocks=True)
+            r["us_per_search"] = r["ms_per_step"] * 1e3
             r.pop("_roof", None)
             r["tensor_frac_bf16_burst"] = r.get("tflops", 0.0) / bf16_peak
             r["hbm_frac"] = r.get("hbm_gbs", 0.0) / peaks["hbm_gbs"]

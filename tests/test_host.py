@@ -68,3 +68,38 @@ def test_raft_select_gold_plus_distractors():
     r = b2r.FlatRetriever(_FakeIndex(np.zeros((3, 6), np.float32), I), [f"p{i}" for i in range(40)])
     docs = r.retrieve_raft(np.zeros((3, 4), np.float32), gold, k=4, k_prime=6, seed=3)
     assert [len(d) for d in docs] == [4, 4, 4] and "p2" in docs[0] and "p33" in docs[1]
+
+
+def test_oracle_rescore_rows_orders_by_global_id(oracle):
+    """bench.py's full-size parity check hands the oracle candidate rows with their own global ids."""
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((400, 48)).astype(np.float32)
+    x[300] = x[9]                                      # a tie: the lower GLOBAL id must come first
+    q = x[9].copy()
+    D0, I0 = oracle.search_defined(x, q[None], 6, 0)
+    sel = np.unique(np.concatenate([I0[0], rng.integers(0, 400, 40)]))[::-1].copy()     # any order
+    D, I = oracle.rescore_rows(x[sel], sel, q, 6, 0)
+    assert np.array_equal(I, I0[0]) and np.array_equal(D.view(np.uint32), D0[0].view(np.uint32))
+    assert list(I[:2]) == [9, 300]
+
+
+def test_bench_rows_do_not_depend_on_the_sharding():
+    """bench.py generates the corpus per 65536-row block: any shard of it sees the same rows (all distributions)."""
+    import torch
+    import bench
+    dev = torch.device("cpu")
+    for dist in ("gauss", "mixture", "dup"):
+        whole = bench.gen_rows(torch, 0, 65000, 1500, 32, dev, dist)
+        parts = torch.cat([bench.gen_rows(torch, 0, 65000, 700, 32, dev, dist), bench.gen_rows(torch, 0, 65700, 800, 32, dev, dist)])
+        assert torch.equal(whole, parts)
+    dup = bench.gen_rows(torch, 0, 0, 200, 32, dev, "dup")
+    assert torch.equal(dup[99], dup[49]) and torch.equal(dup[199], dup[149])       # 1 % exact duplicates
+    q = bench.gen_queries(torch, 8, 32, dev, "mixture", 5000)
+    assert q.shape == (8, 32)
+
+
+def test_bench_reads_traffic_from_the_committed_ncu_capture():
+    import bench
+    traffic, src = bench.ncu_traffic("exact", 1024, bench.N_ROWS, 1)
+    assert src and src.startswith("profiles/") and 3.0e9 < traffic < 3.6e9          # ~1.05x the 3.07 GB corpus
+    assert bench.ncu_traffic("exact", 1024, 12345, 1) == (None, None)
