@@ -60,6 +60,12 @@ def test_argument_validation_needs_no_device():
     assert L.b2r_merge_packed(0, 0, 1, 1, None, None, None, 0, None) == -1
     assert L.b2r_merge_packed(0, 2, 1, 5000, None, None, None, 0, None) == -5
     assert L.b2r_normalize_l2(-1, 8, None, 0, None) == -1
+    assert L.b2r_merge_packed(0, 2000, 1, 1, None, None, None, 0, None) == -5        # more lists than the merge takes
+    # row-sharded entry points: argument errors come before any device or NCCL work
+    assert L.b2r_index_search_sharded(None, 1, None, 1, 0, None, None, None) == -1
+    assert L.b2r_index_set_comm(None, None, 0, 1, 0) == -1
+    assert L.b2r_index_comm_init(None, None, 0, 1, 0) == -1
+    assert L.b2r_nccl_unique_id(None) == -1
 
 
 def test_python_host_raises_not_falls_back():
