@@ -904,6 +904,7 @@ static NcclApi* nccl_api() {
   return api.h ? &api : nullptr;
 }
 constexpr int kNcclUint64 = 5;   // ncclDataType_t ncclUint64
+constexpr int kNcclFloat32 = 7;  // ncclDataType_t ncclFloat32
 
 static void comm_release(b2r_index* idx) {
   if (idx->comm && idx->comm_owned) {
@@ -979,7 +980,7 @@ extern "C" int b2r_index_search_sharded(b2r_index* idx, int64_t nq, const float*
   NcclApi* n = idx->world > 1 ? nccl_api() : nullptr;
   DeviceGuard g(idx->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool out_dev = is_device_ptr(D);
+  const bool out_dev = is_device_ptr(D), q_dev = is_device_ptr(q);
   if (out_dev != is_device_ptr(I)) return fail(B2R_ERR_ARG, "D and I must both be host or both be device pointers");
   const int64_t mb = std::min(nq, kSearchBatch);
   // handle-owned, persistent: this rank's packed top-k and the gathered [world][batch*k] lists
@@ -993,7 +994,21 @@ extern "C" int b2r_index_search_sharded(b2r_index* idx, int64_t nq, const float*
   uint64_t* all = static_cast<uint64_t*>(idx->shard_all.p);
   for (int64_t q0 = 0; q0 < nq; q0 += kSearchBatch) {
     const int64_t m = std::min(kSearchBatch, nq - q0);
-    RC_TRY(search_batch(idx, m, q + q0 * idx->d, k, normalize_queries, idx->row_offset, nullptr, nullptr, local, st, q0 == 0));
+    const float* qb = q + q0 * idx->d;
+    if (!q_dev && idx->world > 1 && m >= 16 * idx->world) {
+      // Host queries: every rank holds the same rows, so each uploads only ITS 1/G of them over PCIe and the ranks
+      // exchange the slices over NVLink (an in-place all-gather), instead of G full uploads from one host at once.
+      const int64_t per = (m + idx->world - 1) / idx->world;
+      RC_TRY(idx->stage_q.ensure(size_t(per) * idx->world * idx->d * 4));
+      float* sq = static_cast<float*>(idx->stage_q.p);
+      const int64_t r0 = std::min<int64_t>(m, per * idx->rank), r1 = std::min<int64_t>(m, r0 + per);
+      if (r1 > r0)
+        CU_TRY(cudaMemcpyAsync(sq + r0 * idx->d, qb + r0 * idx->d, size_t(r1 - r0) * idx->d * 4, cudaMemcpyHostToDevice, st));
+      const int r = n->AllGather(sq + per * idx->rank * idx->d, sq, size_t(per) * idx->d, kNcclFloat32, idx->comm, st);
+      if (r != 0) return fail(B2R_ERR_CUDA, "ncclAllGather (queries) failed: %s", n->GetErrorString(r));
+      qb = sq;
+    }
+    RC_TRY(search_batch(idx, m, qb, k, normalize_queries, idx->row_offset, nullptr, nullptr, local, st, q0 == 0));
     const uint64_t* lists = local;
     if (idx->world > 1) {
       const int r = n->AllGather(local, all, size_t(m) * k, kNcclUint64, idx->comm, st);   // the single collective
@@ -1008,6 +1023,8 @@ extern "C" int b2r_index_search_sharded(b2r_index* idx, int64_t nq, const float*
       CU_TRY(cudaMemcpyAsync(D + q0 * k, Dd, size_t(m) * k * 4, cudaMemcpyDeviceToHost, st));
       CU_TRY(cudaMemcpyAsync(I + q0 * k, Id, size_t(m) * k * 8, cudaMemcpyDeviceToHost, st));
       CU_TRY(cudaStreamSynchronize(st));
+    } else if (!q_dev) {
+      CU_TRY(cudaStreamSynchronize(st));          // the caller's host query buffer is free again on return
     }
   }
   idx->searched = true;
