@@ -13,16 +13,24 @@
 //                                (CTA, query) candidate buffer
 //   warps 6..9  splitter       : 3xTF32 only: x_lo = x - trunc_tf32(x) on every landed corpus stage
 // Work item (t, m) = corpus rows [256t, 256t+256) x queries [128m, 128m+128), t-major, dealt round-robin to the
-// CTAs so that the re-reads of a corpus tile by the other query tiles hit L2.
+// CTAs so that the re-reads of a corpus tile by the other query tiles hit L2.  kPair (fp32 rows, >= 2 query tiles):
+// two CTAs of a cluster share one M=256 cta_group::2 MMA, each staging half of the corpus tile; whole tiles are
+// dealt to the pairs (see the kernel).
 //
 // Running top-K': threshold + append buffer (cap entries per (CTA, query), interleaved [entry][lane] so that a
-// warp's accesses coalesce).  Thresholds are SEEDED: a first launch of this kernel covers the first S rows, one
-// seed tile per (CTA, query tile), and finds each query's threshold by bisection over the 256 scores while they
-// still sit in TMEM (no memory traffic); seed_select_kernel turns the seed candidates into the exact K'-th best
-// of those rows; the main launch filters with it.  When a buffer is nearly full the owning lane selects a new
-// threshold by bisection on the packed keys (lane-parallel), keeps [K', kmax] entries and publishes the bound
-// with a global atomicMax, so all CTAs filter with the best bound any of them has found.  A published bound is
-// always the K'-th best score of a real subset of rows, hence a valid lower bound of the final K'-th best.
+// warp's accesses coalesce).  Where the thresholds come from, by launch mode:
+//   single    (corpus of at most one tile per CTA) bisection over the 256 scores while they sit in TMEM;
+//   sampling  a first launch scores S tiles spread over the shard and keeps only the J best scores of every
+//             (tile, query); seed_thr_kernel takes the K'-th largest of them per query; the MAIN launch then
+//             covers every row (the sampled ones again) and filters with it;
+//   rounds    very large shards: the main scan runs in rounds of 8x growing size, tighten_thr_kernel raises the
+//             thresholds to the K'-th best of everything found so far in between;
+//   range     fixed thresholds handed over by finalize for the queries its proof could not settle (no compaction:
+//             every row that reaches the bound is kept, an overflowing buffer raises a flag).
+// When a buffer is nearly full the owning lane selects a new threshold by bisection on the packed keys
+// (lane-parallel), keeps [K', kmax] entries and publishes the bound with a global atomicMax, so all CTAs filter
+// with the best bound any of them has found.  A published bound is always the K'-th best score of a real subset
+// of rows, hence a valid lower bound of the final K'-th best.
 //
 // Algorithmic HBM bytes per search: rows * ld * sizeof(elem) (the corpus shard, once).
 // Algorithmic flops: 2 * nq * rows * d.
