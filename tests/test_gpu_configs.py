@@ -140,6 +140,22 @@ def test_multi_round_scan_of_a_large_shard(oracle, monkeypatch, storage, nq):
     assert st["unverified"] == 0 and st["launches"] >= 10      # prep, sample, thr, 2 rounds + tightening, merge, hand-over chain
 
 
+@pytest.mark.parametrize("nq,metric,k", [(800, b2r.METRIC_L2, 10), (512, b2r.METRIC_INNER_PRODUCT, 21), (2300, b2r.METRIC_INNER_PRODUCT, 5)])
+def test_cta_pair_kernel_shapes(oracle, nq, metric, k):
+    """fp32 rows with several query tiles run on the CTA-pair kernel (cta_group::2): an odd number of query tiles
+    (800 queries = 7 tiles, the last pair half empty), the L2 metric (row norms shared by the pair), K' = 42, and a
+    call of two launches whose second holds a single query tile."""
+    x, q = _data(oracle, 70_000, 96, nq, 64)
+    x[40_000:40_040] = x[5]                         # a tie cluster for query 3: hand-over from the pair kernel's buffers
+    q[3] = x[5]
+    idx = b2r.IndexFlat(96, metric)
+    idx.add(x)
+    D, I = idx.search(q, k)
+    _check(D, I, *oracle.search_ref(x, q, k, metric, extra=128))
+    st = idx.last_stats()
+    assert st["engine"] == b2r.ENGINE_UMMA and st["unverified"] == 0 and st["fallback_queries"] >= 1
+
+
 def test_fallback_counters_add_up_over_query_batches(oracle):
     """A call of more than 8192 queries is walked in batches; an unproven query in the second batch is handled
     there and the counters of the batches add up on the device (no read-back between them)."""
