@@ -156,6 +156,26 @@ def test_cta_pair_kernel_shapes(oracle, nq, metric, k):
     assert st["engine"] == b2r.ENGINE_UMMA and st["unverified"] == 0 and st["fallback_queries"] >= 1
 
 
+@pytest.mark.parametrize("storage", ["f32", "bf16"])
+def test_every_query_of_a_large_batch_is_handed_over(oracle, storage):
+    """2500 queries that all hit a cluster of 60 identical rows: none can be proven by the first pass, so the range
+    list holds 2500 entries — more than one scoring launch takes (2048), i.e. two range launches and a merge that
+    strides over both chunks of the candidate scratch."""
+    x, _ = _data(oracle, 30_000, 64, 4, 65)
+    x[2000:2060] = x[1]
+    rng = np.random.default_rng(66)
+    q = np.tile(x[1], (2500, 1)) + 1e-3 * rng.standard_normal((2500, 64)).astype(np.float32)
+    q = oracle.normalize(q.astype(np.float32))
+    idx = b2r.IndexFlatIP(64, storage=storage)
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    xo, qo = (oracle.round_bf16(x), oracle.round_bf16(q)) if storage == "bf16" else (x, q)
+    _check(D, I, *oracle.search_ref(xo, qo, 10, 0, extra=128))
+    st = idx.last_stats()
+    assert st["fallback_queries"] == 2500 and st["exhaustive_queries"] == 0 and st["unverified"] == 0
+    assert set(I[:, :10].ravel()) <= {1} | set(range(2000, 2060))
+
+
 def test_fallback_counters_add_up_over_query_batches(oracle):
     """A call of more than 8192 queries is walked in batches; an unproven query in the second batch is handled
     there and the counters of the batches add up on the device (no read-back between them)."""
