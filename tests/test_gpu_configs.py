@@ -176,6 +176,24 @@ def test_every_query_of_a_large_batch_is_handed_over(oracle, storage):
     assert set(I[:, :10].ravel()) <= {1} | set(range(2000, 2060))
 
 
+def test_second_range_pass_settles_what_the_first_cannot_hold(oracle):
+    """3000 near-copies of one row at distances spread up to 0.08: the 1xTF32 range pass's band (4e-3) holds all of
+    them and overflows, the 3xTF32 pass's band (1.4e-4) holds a few hundred — the query is settled there, without
+    the exhaustive scan."""
+    x, q = _data(oracle, 40_000, 128, 20, 67)
+    rng = np.random.default_rng(68)
+    noise = oracle.normalize(rng.standard_normal((3000, 128)).astype(np.float32))
+    radius = rng.uniform(0.0, 0.08, (3000, 1)).astype(np.float32)
+    x[5000:8000] = oracle.normalize((x[3][None, :] + radius * noise).astype(np.float32))
+    q[7] = x[3]
+    idx = b2r.IndexFlatIP(128)
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    _check(D, I, *oracle.search_ref(x, q, 10, 0, extra=4000))
+    st = idx.last_stats()
+    assert st["fallback_queries"] >= 1 and st["exhaustive_queries"] == 0 and st["unverified"] == 0
+
+
 def test_fallback_counters_add_up_over_query_batches(oracle):
     """A call of more than 8192 queries is walked in batches; an unproven query in the second batch is handled
     there and the counters of the batches add up on the device (no read-back between them)."""
