@@ -17,8 +17,8 @@
 //      superset of the true top-k that needs no gap — and finalize_range_kernel re-scores and orders it.
 //      If that set does not fit its buffers (thousands of rows tied with the k-th score) the query goes on
 //      to the exhaustive DOT64 scan (score_exact.cuh), which cannot fail.  No host round trip anywhere.
-// The same gather merges the all-gathered [G,nq,k] packed lists (merge_packed_kernel) and selects the seed
-// thresholds of the tcgen05 engine (seed_select_kernel in score_umma.cuh).
+// The same gather merges the all-gathered [G,nq,k] packed lists (merge_packed_kernel) and tightens the thresholds
+// between the rounds of a very large shard's scan (tighten_thr_kernel in score_umma.cuh).
 #pragma once
 #include <float.h>
 #include "common.cuh"
