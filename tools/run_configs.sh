@@ -4,7 +4,7 @@ N=$1; TAG=$2
 run() {  # name, extra args
   local name=$1; shift
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 \
-    bench.py --gpus $N --steps 5 --warmup 3 --no-cpu --sweep= "$@" > gpurun_out/${TAG}_${name}_n$N.log 2>&1
+    bench.py --gpus $N --steps 5 --warmup 3 --no-cpu --sweep= --extras= --scale-configs= "$@" > gpurun_out/${TAG}_${name}_n$N.log 2>&1
   tail -1 gpurun_out/${TAG}_${name}_n$N.log | python -c "
 import json,sys
 try:
